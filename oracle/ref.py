@@ -1,0 +1,320 @@
+"""oracle/ref.py -- TEST INFRASTRUCTURE, not product code.
+
+ctypes binding of oracle/_ref/libdqmc_ref.so: the reference's own hot-path sources compiled
+unmodified (oracle/Makefile) behind the C harness oracle/ref_harness.cpp.  Used to pin
+oracle/dqmc_oracle.py, to generate tests/golden/*.npz, and as bench.py's CPU baseline
+(`cpu_baseline.kind == "reference"`).  The .so is git-ignored but travels to the GPU box.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "_ref", "libdqmc_ref.so")
+_lib = None
+
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int)
+_llp = C.POINTER(C.c_longlong)
+
+
+def build(reference_root: str = "/root/reference", force: bool = False) -> bool:
+    """Compile oracle/_ref when the reference tree is present (this container only)."""
+    if os.path.exists(LIB_PATH) and not force:
+        return True
+    if not os.path.isdir(reference_root):
+        return False
+    subprocess.check_call(["make", "-C", _HERE, f"REF={reference_root}"], stdout=subprocess.DEVNULL)
+    return os.path.exists(LIB_PATH)
+
+
+def available() -> bool:
+    return os.path.exists(LIB_PATH)
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not available():
+            raise RuntimeError("oracle/_ref/libdqmc_ref.so missing: run `make -C oracle` where /root/reference exists")
+        import scipy.linalg  # noqa: F401  (makes sure libscipy_openblas is resolvable/loaded)
+
+        L = C.CDLL(LIB_PATH)
+        L.ref_create.restype = C.c_void_p
+        L.ref_create.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int, C.c_uint]
+        for name in ("ref_g", "ref_logdet", "ref_acc_rate", "ref_max_err", "ref_mean_err", "ref_global_action"):
+            getattr(L, name).restype = C.c_double
+            getattr(L, name).argtypes = [C.c_void_p]
+        L.ref_local_update.restype = C.c_double
+        L.ref_local_update.argtypes = [C.c_void_p, C.c_int]
+        L.ref_inv_I_plus_ldr.restype = C.c_double
+        L.ref_run_sweeps.restype = C.c_double
+        L.ref_run_sweeps.argtypes = [C.POINTER(C.c_void_p), C.c_int, C.c_int]
+        L.ref_replica_exchange.argtypes = [C.POINTER(C.c_void_p), C.c_int]
+        _lib = L
+    return _lib
+
+
+def _d(a):
+    return a.ctypes.data_as(_dp)
+
+
+def _colmajor(a: np.ndarray) -> np.ndarray:
+    """numpy [row, col] -> contiguous buffer in column-major order."""
+    return np.ascontiguousarray(np.asarray(a, dtype=np.float64).T)
+
+
+def _from_colmajor(buf: np.ndarray) -> np.ndarray:
+    return buf.T.copy()
+
+
+class RefSim:
+    """One reference chain: AttractiveHubbard + DQMC + GF + LDRStack built exactly as
+    source/main.cpp:85-106 does, with an injected seed."""
+
+    def __init__(self, L1, L2, U, t, mu, beta, nt, n_stab, seed):
+        self.L = lib()
+        self.h = C.c_void_p(self.L.ref_create(L1, L2, U, t, mu, beta, nt, n_stab, seed))
+        if not self.h:
+            raise RuntimeError("ref_create failed")
+        self.ns = self.L.ref_ns(self.h)
+        self.nt = self.L.ref_nt(self.h)
+        self.n_stack = self.L.ref_n_stack(self.h)
+        self.n_stab = n_stab
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.L.ref_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+    # --- state ---
+    @property
+    def g(self):
+        return self.L.ref_g(self.h)
+
+    def fields(self) -> np.ndarray:
+        """fields[l, site] (int64)."""
+        buf = np.empty((self.ns, self.nt), dtype=np.int64)  # column-major nt x N
+        self.L.ref_get_fields(self.h, buf.ctypes.data_as(_llp))
+        return buf.T.copy()
+
+    def set_fields(self, f: np.ndarray, reinit: bool = True):
+        buf = np.ascontiguousarray(np.asarray(f, dtype=np.int64).T)
+        self.L.ref_set_fields(self.h, buf.ctypes.data_as(_llp))
+        if reinit:
+            self.L.ref_init(self.h)
+
+    def reseed(self, seed: int):
+        self.L.ref_reseed(self.h, seed)
+
+    def _mat(self, fn, *args) -> np.ndarray:
+        buf = np.empty((self.ns, self.ns))
+        fn(self.h, *args, _d(buf))
+        return _from_colmajor(buf)
+
+    def expK(self):
+        return self._mat(self.L.ref_get_expK)
+
+    def invexpK(self):
+        return self._mat(self.L.ref_get_invexpK)
+
+    def expK_half(self):
+        return self._mat(self.L.ref_get_expK_half)
+
+    def invexpK_half(self):
+        return self._mat(self.L.ref_get_invexpK_half)
+
+    def G(self, l: int) -> np.ndarray:
+        buf = np.empty((self.ns, self.ns))
+        if self.L.ref_get_G(self.h, l, _d(buf)) != 0:
+            raise IndexError(f"Gtt[{l}] not populated")
+        return _from_colmajor(buf)
+
+    def set_G(self, l: int, G: np.ndarray):
+        self.L.ref_set_G(self.h, l, _d(_colmajor(G)))
+
+    def logdet(self):
+        return self.L.ref_logdet(self.h)
+
+    def stack(self, i: int):
+        Lb = np.empty((self.ns, self.ns))
+        d = np.empty(self.ns)
+        Rb = np.empty((self.ns, self.ns))
+        self.L.ref_get_stack(self.h, i, _d(Lb), _d(d), _d(Rb))
+        return _from_colmajor(Lb), d, _from_colmajor(Rb)
+
+    def set_stack(self, i, Lm, d, Rm):
+        self.L.ref_set_stack(self.h, i, _d(_colmajor(Lm)), _d(np.ascontiguousarray(d, dtype=np.float64)), _d(_colmajor(Rm)))
+
+    # --- steps ---
+    def init(self):
+        self.L.ref_init(self.h)
+
+    def sweep_fwd(self):
+        self.L.ref_sweep_fwd(self.h)
+
+    def sweep_bwd(self):
+        self.L.ref_sweep_bwd(self.h)
+
+    def local_update(self, l: int) -> float:
+        return self.L.ref_local_update(self.h, l)
+
+    def local_update_ratio(self, l, i, new):
+        R = C.c_double()
+        dl = C.c_double()
+        self.L.ref_local_update_ratio(self.h, l, i, new, C.byref(R), C.byref(dl))
+        return R.value, dl.value
+
+    def update_greens_local(self, delta, l, i):
+        self.L.ref_update_greens_local(self.h, C.c_double(delta), l, i)
+
+    def wrap_fwd(self, l):
+        self.L.ref_wrap_fwd(self.h, l)
+
+    def wrap_bwd(self, l):
+        self.L.ref_wrap_bwd(self.h, l)
+
+    def Bbar(self, i_stack):
+        return self._mat(self.L.ref_Bbar, i_stack)
+
+    def expV(self, l):
+        out = np.empty(self.ns)
+        self.L.ref_expV(self.h, l, _d(out))
+        return out
+
+    def update_stack_fwd(self, i, Bbar):
+        self.L.ref_update_stack_fwd(self.h, i, _d(_colmajor(Bbar)))
+
+    def update_stack_bwd(self, i, Bbar):
+        self.L.ref_update_stack_bwd(self.h, i, _d(_colmajor(Bbar)))
+
+    def stabilize_fwd(self, l):
+        self.L.ref_stabilize_fwd(self.h, l)
+
+    def stabilize_bwd(self, l):
+        self.L.ref_stabilize_bwd(self.h, l)
+
+    def half_wrap(self):
+        return self._mat(self.L.ref_half_wrap)
+
+    def global_action(self):
+        return self.L.ref_global_action(self.h)
+
+    def observables(self):
+        out3 = np.empty(3)
+        corr = np.empty((self.ns, self.ns))
+        self.L.ref_observables(self.h, _d(out3), _d(corr))
+        return out3[0], out3[1], out3[2], _from_colmajor(corr)
+
+    def acc_rate(self):
+        return self.L.ref_acc_rate(self.h)
+
+    def max_err(self):
+        return self.L.ref_max_err(self.h)
+
+    def mean_err(self):
+        return self.L.ref_mean_err(self.h)
+
+    def rng_tape(self, n_calls: int, advance: bool = False):
+        """(perm, k, u), each [n_calls, N]: the draws the next n_calls local_update calls make."""
+        perm = np.empty((n_calls, self.ns), dtype=np.int32)
+        k = np.empty((n_calls, self.ns), dtype=np.int32)
+        u = np.empty((n_calls, self.ns), dtype=np.float64)
+        self.L.ref_rng_tape(self.h, n_calls, int(advance), perm.ctypes.data_as(_ip), k.ctypes.data_as(_ip), _d(u))
+        return perm, k, u
+
+
+def mt19937_raw(seed: int, n: int) -> np.ndarray:
+    out = np.empty(n, dtype=np.uint32)
+    lib().ref_mt19937_raw(C.c_uint(seed), n, out.ctypes.data_as(C.POINTER(C.c_uint)))
+    return out
+
+
+def _ldr_bufs(n):
+    return np.empty((n, n)), np.empty(n), np.empty((n, n))
+
+
+def to_LDR(M):
+    n = M.shape[0]
+    Lb, d, Rb = _ldr_bufs(n)
+    if lib().ref_to_LDR(n, _d(_colmajor(M)), _d(Lb), _d(d), _d(Rb)) != 0:
+        raise RuntimeError("QR decomposition failed in to_LDR")
+    return _from_colmajor(Lb), d, _from_colmajor(Rb)
+
+
+def _in(F):
+    Lm, d, Rm = F
+    return _d(_colmajor(Lm)), _d(np.ascontiguousarray(d, dtype=np.float64)), _d(_colmajor(Rm))
+
+
+def mat_mul_ldr(M, F):
+    n = M.shape[0]
+    Lb, d, Rb = _ldr_bufs(n)
+    keep = (_colmajor(M), _colmajor(F[0]), np.ascontiguousarray(F[1], dtype=np.float64), _colmajor(F[2]))
+    lib().ref_mat_mul_ldr(n, _d(keep[0]), _d(keep[1]), _d(keep[2]), _d(keep[3]), _d(Lb), _d(d), _d(Rb))
+    return _from_colmajor(Lb), d, _from_colmajor(Rb)
+
+
+def ldr_mul_mat(F, M):
+    n = M.shape[0]
+    Lb, d, Rb = _ldr_bufs(n)
+    keep = (_colmajor(F[0]), np.ascontiguousarray(F[1], dtype=np.float64), _colmajor(F[2]), _colmajor(M))
+    lib().ref_ldr_mul_mat(n, _d(keep[0]), _d(keep[1]), _d(keep[2]), _d(keep[3]), _d(Lb), _d(d), _d(Rb))
+    return _from_colmajor(Lb), d, _from_colmajor(Rb)
+
+
+def ldr_mul_ldr(F1, F2):
+    n = F1[0].shape[0]
+    Lb, d, Rb = _ldr_bufs(n)
+    k = (_colmajor(F1[0]), np.ascontiguousarray(F1[1], dtype=np.float64), _colmajor(F1[2]),
+         _colmajor(F2[0]), np.ascontiguousarray(F2[1], dtype=np.float64), _colmajor(F2[2]))
+    lib().ref_ldr_mul_ldr(n, *[_d(x) for x in k], _d(Lb), _d(d), _d(Rb))
+    return _from_colmajor(Lb), d, _from_colmajor(Rb)
+
+
+def inv_I_plus_ldr(F):
+    n = F[0].shape[0]
+    G = np.empty((n, n))
+    k = (_colmajor(F[0]), np.ascontiguousarray(F[1], dtype=np.float64), _colmajor(F[2]))
+    logdet = lib().ref_inv_I_plus_ldr(n, *[_d(x) for x in k], _d(G))
+    return _from_colmajor(G), logdet
+
+
+def inv_I_plus_ldr_mul_ldr(F1, F2):
+    n = F1[0].shape[0]
+    G = np.empty((n, n))
+    k = (_colmajor(F1[0]), np.ascontiguousarray(F1[1], dtype=np.float64), _colmajor(F1[2]),
+         _colmajor(F2[0]), np.ascontiguousarray(F2[1], dtype=np.float64), _colmajor(F2[2]))
+    lib().ref_inv_I_plus_ldr_mul_ldr(n, *[_d(x) for x in k], _d(G))
+    return _from_colmajor(G)
+
+
+def inv_invldr_plus_ldr(F1, F2):
+    n = F1[0].shape[0]
+    G = np.empty((n, n))
+    k = (_colmajor(F1[0]), np.ascontiguousarray(F1[1], dtype=np.float64), _colmajor(F1[2]),
+         _colmajor(F2[0]), np.ascontiguousarray(F2[1], dtype=np.float64), _colmajor(F2[2]))
+    lib().ref_inv_invldr_plus_ldr(n, *[_d(x) for x in k], _d(G))
+    return _from_colmajor(G)
+
+
+def partner_rank(rank, world_size, attempt):
+    return lib().ref_partner_rank(rank, world_size, attempt)
+
+
+def replica_exchange(sims: list[RefSim]):
+    arr = (C.c_void_p * len(sims))(*[s.h for s in sims])
+    lib().ref_replica_exchange(arr, len(sims))
+
+
+def run_sweeps(sims: list[RefSim], n_sweeps: int) -> float:
+    """Times n_sweeps full sweeps on every chain, one host thread per chain.  Returns seconds."""
+    arr = (C.c_void_p * len(sims))(*[s.h for s in sims])
+    return lib().ref_run_sweeps(arr, len(sims), n_sweeps)

@@ -1,0 +1,1066 @@
+// dqmcb.cu -- kernels and C ABI (include/dqmc_b200.h) of the B200-native DQMC sweep hot path.
+//
+// One CTA per walker (Markov chain); W walkers batched per launch.  See DESIGN.md for the kernel
+// inventory and rooflines.  Compiled for sm_100a only; there is no CPU fallback in this library.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "dqmcb_internal.cuh"
+#include "engine.cuh"
+#include "fast64.cuh"
+
+using namespace dq;
+
+// =====================================================================================================
+// kernels (generic N)
+// =====================================================================================================
+
+// Propagate + Metropolis over `n_slices` consecutive slices starting at l_first, in sweep direction
+// dir (+1: wrap then flip, source/dqmc.cpp:357-366; -1: flip then wrap, source/dqmc.cpp:416-426).
+// flags: bit0 = do wraps, bit1 = do flips.
+__global__ void __launch_bounds__(kThreads) k_propagate(Params p, int l_first, int n_slices, int dir, unsigned long long visit0, int flags) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int w = blockIdx.x, n = p.N;
+    // small arrays
+    double* s_ev = reinterpret_cast<double*>(smem);
+    double* s_iev = s_ev + n;
+    double* s_u = s_iev + n;
+    double* s_ucol = s_u + n;
+    double* s_vrow = s_ucol + n;
+    int* s_perm = reinterpret_cast<int*>(s_vrow + n);
+    int* s_k = s_perm + n;
+    uint32_t* s_key = reinterpret_cast<uint32_t*>(s_k + n);
+    int8_t* s_f = reinterpret_cast<int8_t*>(s_key + n);
+    size_t off = (size_t)(5 * n) * 8 + (size_t)(3 * n) * 4 + (size_t)n;
+    off = (off + 15) & ~(size_t)15;
+    double* tiles = reinterpret_cast<double*>(smem + off);
+    double* gws = p.ws + (size_t)w * 3 * n * p.LD;
+    double* g = (p.smem_mats_prop >= 1) ? tiles : gws;
+    double* t = (p.smem_mats_prop >= 2) ? tiles + (size_t)n * p.LD : gws + (size_t)n * p.LD;
+    const int ld = p.LD;
+    double* Gg = p.G + (size_t)w * n * n;
+    cta_copy(g, ld, Gg, n, n);
+    __syncthreads();
+    int accepted = 0;
+    for (int s = 0; s < n_slices; ++s) {
+        const int l = l_first + dir * s;
+        int8_t* fl = p.fields + ((size_t)w * p.nt + l) * n;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) s_f[i] = fl[i];
+        __syncthreads();
+        if (dir > 0 && (flags & 1)) {
+            for (int i = threadIdx.x; i < n; i += blockDim.x) {
+                s_ev[i] = p.lut_ev[s_f[i]];
+                s_iev[i] = p.lut_iev[s_f[i]];
+            }
+            __syncthreads();
+            dev_wrap_forward(p, n, g, ld, t, ld, s_ev, s_iev);
+        }
+        if (flags & 2) {
+            load_visit_draws(p, w, visit0 + s, s_perm, s_k, s_u, s_key);
+            accepted += dev_local_update(p, n, g, ld, s_f, s_perm, s_k, s_u, s_ucol, s_vrow);
+            __syncthreads();
+            for (int i = threadIdx.x; i < n; i += blockDim.x) fl[i] = s_f[i];
+        }
+        if (dir < 0 && (flags & 1)) {
+            for (int i = threadIdx.x; i < n; i += blockDim.x) {
+                s_ev[i] = p.lut_ev[s_f[i]];
+                s_iev[i] = p.lut_iev[s_f[i]];
+            }
+            __syncthreads();
+            dev_wrap_backward(p, n, g, ld, t, ld, s_ev, s_iev);
+        }
+    }
+    __syncthreads();
+    cta_copy(Gg, n, g, ld, n);
+    if (threadIdx.x == 0) p.accepted[w] += (unsigned long long)accepted;
+}
+
+// calculate_Bbar into the global Bbar buffer (stand-alone step for parity tests)
+__global__ void __launch_bounds__(kThreads) k_bbar(Params p, int i_stack) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    Work wk;
+    carve(wk, p, blockIdx.x, p.smem_mats_stab, smem);
+    dev_bbar(p, wk, blockIdx.x, i_stack);
+    __syncthreads();
+    cta_copy(p.Bbar + (size_t)blockIdx.x * p.N * p.N, p.N, wk.b[0], wk.ld[0], p.N);
+}
+
+__device__ inline double* stkL(const Params& p, int w, int i) { return p.stackL + ((size_t)w * p.n_stack + i) * p.N * p.N; }
+__device__ inline double* stkR(const Params& p, int w, int i) { return p.stackR + ((size_t)w * p.n_stack + i) * p.N * p.N; }
+__device__ inline double* stkD(const Params& p, int w, int i) { return p.stackD + ((size_t)w * p.n_stack + i) * p.N; }
+
+__device__ inline void store_d(double* dst, const double* src, int n) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
+}
+
+// End-of-block work of the sweeps (source/dqmc.cpp:369-394 forward, 429-454 backward):
+// Bbar from the current fields, stack update, stabilised G, check_error against the wrapped G.
+__global__ void __launch_bounds__(kThreads) k_stabilize(Params p, int l, int dir) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int w = blockIdx.x, n = p.N;
+    Work wk;
+    carve(wk, p, w, p.smem_mats_stab, smem);
+    const int i = l / p.n_stab;
+    dev_bbar(p, wk, w, i);  // -> b[0]
+    double *b0 = wk.b[0], *b1 = wk.b[1], *b2 = wk.b[2];
+    const int l0 = wk.ld[0], l1 = wk.ld[1], l2 = wk.ld[2];
+    __syncthreads();
+    if (dir > 0) {
+        // update_stack_forward (source/dqmc.cpp:134-146)
+        if (i == 0) {
+            dev_to_ldr(wk, n, b0, l0, b1, l1, b2, l2, wk.dnew);
+            cta_copy(stkL(p, w, i), n, b1, l1, n);
+            cta_copy(stkR(p, w, i), n, b2, l2, n);
+        } else {
+            // mat_mul_ldr (source/stablelinalg.cpp:69-79): (Bbar L) D -> QR ; R <- R_new R_old
+            store_d(wk.sv[0], stkD(p, w, i - 1), n);
+            __syncthreads();
+            cta_gemm<false>(b1, l1, b0, 1, l0, stkL(p, w, i - 1), 1, n, n, nullptr, wk.sv[0]);
+            dev_to_ldr(wk, n, b1, l1, b0, l0, b2, l2, wk.dnew);
+            cta_gemm<false>(stkR(p, w, i), n, b2, 1, l2, stkR(p, w, i - 1), 1, n, n, nullptr, nullptr);
+            cta_copy(stkL(p, w, i), n, b0, l0, n);
+        }
+    } else {
+        // update_stack_backward (source/dqmc.cpp:189-201)
+        if (i == p.n_stack - 1) {
+            dev_to_ldr(wk, n, b0, l0, b1, l1, b2, l2, wk.dnew);
+            cta_copy(stkL(p, w, i), n, b1, l1, n);
+            cta_copy(stkR(p, w, i), n, b2, l2, n);
+        } else {
+            // ldr_mul_mat (source/stablelinalg.cpp:57-67): D (R Bbar) -> QR ; L <- L_old Q
+            store_d(wk.sv[0], stkD(p, w, i + 1), n);
+            __syncthreads();
+            cta_gemm<false>(b1, l1, stkR(p, w, i + 1), 1, n, b0, 1, l0, n, wk.sv[0], nullptr);
+            dev_to_ldr(wk, n, b1, l1, b0, l0, b2, l2, wk.dnew);
+            cta_gemm<false>(stkL(p, w, i), n, stkL(p, w, i + 1), 1, n, b0, 1, l0, n, nullptr, nullptr);
+            cta_copy(stkR(p, w, i), n, b2, l2, n);
+        }
+    }
+    store_d(stkD(p, w, i), wk.dnew, n);
+    __syncthreads();  // stack entry i visible to the whole CTA (global writes + barrier)
+    // stabilize_GF_* (source/dqmc.cpp:148-161, 203-215)
+    const double* Gnew;
+    int ldn;
+    const bool at_end = (dir > 0) ? (l == p.nt - 1) : (l == 0);
+    if (at_end) {
+        const double ld_ = dev_inv_I_plus_ldr(p, wk, n, stkL(p, w, i), n, stkD(p, w, i), stkR(p, w, i), n);
+        if (threadIdx.x == 0) p.logdet[w] = ld_;
+        Gnew = b1;
+        ldn = l1;
+    } else if (dir > 0) {
+        dev_inv_I_plus_ldr_mul_ldr(p, wk, n, stkL(p, w, i), stkD(p, w, i), stkR(p, w, i), stkL(p, w, i + 1), stkD(p, w, i + 1),
+                                   stkR(p, w, i + 1), n);
+        Gnew = b2;
+        ldn = l2;
+    } else {
+        dev_inv_I_plus_ldr_mul_ldr(p, wk, n, stkL(p, w, i - 1), stkD(p, w, i - 1), stkR(p, w, i - 1), stkL(p, w, i), stkD(p, w, i),
+                                   stkR(p, w, i), n);
+        Gnew = b2;
+        ldn = l2;
+    }
+    // check_error (source/dqmc.cpp:317-329) + install the stabilised G
+    double* Gg = p.G + (size_t)w * n * n;
+    double emax = 0.0;
+    for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
+        const int r = e % n, c = e / n;
+        const double v = Gnew[r + (size_t)c * ldn];
+        emax = fmax(emax, fabs(Gg[e] - v));
+        Gg[e] = v;
+    }
+    emax = cta_reduce_max(emax, wk.red);
+    if (threadIdx.x == 0) {
+        p.err_max[w] = fmax(p.err_max[w], emax);
+        p.err_sum[w] += emax;
+        p.err_cnt[w] += 1ull;
+    }
+}
+
+// DQMC::init_stacks (source/dqmc.cpp:43-59): right-hand partial products, top block first
+__global__ void __launch_bounds__(kThreads) k_init_stacks(Params p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int w = blockIdx.x, n = p.N;
+    Work wk;
+    carve(wk, p, w, p.smem_mats_stab, smem);
+    double *b0 = wk.b[0], *b1 = wk.b[1], *b2 = wk.b[2];
+    const int l0 = wk.ld[0], l1 = wk.ld[1], l2 = wk.ld[2];
+    for (int i = p.n_stack - 1; i >= 0; --i) {
+        dev_bbar(p, wk, w, i);
+        __syncthreads();
+        // Bbar_ldr = to_LDR(Bbar): Q -> b1, Rn -> b2, d -> sv[2]
+        dev_to_ldr(wk, n, b0, l0, b1, l1, b2, l2, wk.sv[2]);
+        if (i == p.n_stack - 1) {
+            cta_copy(stkL(p, w, i), n, b1, l1, n);
+            cta_copy(stkR(p, w, i), n, b2, l2, n);
+            store_d(stkD(p, w, i), wk.sv[2], n);
+        } else {
+            // ldr_mul_ldr(stack[i+1], Bbar_ldr) (source/stablelinalg.cpp:81-92)
+            store_d(wk.sv[0], stkD(p, w, i + 1), n);
+            __syncthreads();
+            // M' = D1 (R1 L2) D2 -> b0
+            cta_gemm<false>(b0, l0, stkR(p, w, i + 1), 1, n, b1, 1, l1, n, wk.sv[0], wk.sv[2]);
+            // keep R2 (b2) : factor b0 -> Q in b1 (L2 no longer needed), Rn in global R slot as temp
+            double* Rtmp = stkR(p, w, i);
+            dev_to_ldr(wk, n, b0, l0, b1, l1, Rtmp, n, wk.dnew);
+            // L = L1 Q
+            cta_gemm<false>(stkL(p, w, i), n, stkL(p, w, i + 1), 1, n, b1, 1, l1, n, nullptr, nullptr);
+            // R = R_new R2  (Rtmp -> b0 first, then product into the global slot)
+            cta_copy(b0, l0, Rtmp, n, n);
+            __syncthreads();
+            cta_gemm<false>(Rtmp, n, b0, 1, l0, b2, 1, l2, n, nullptr, nullptr);
+            store_d(stkD(p, w, i), wk.dnew, n);
+        }
+        __syncthreads();
+    }
+}
+
+// DQMC::init_greenfunctions (source/dqmc.cpp:61-72): G(0) = [I + stack[0]]^-1, log_det_M
+__global__ void __launch_bounds__(kThreads) k_init_green(Params p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int w = blockIdx.x, n = p.N;
+    Work wk;
+    carve(wk, p, w, p.smem_mats_stab, smem);
+    const double ld_ = dev_inv_I_plus_ldr(p, wk, n, stkL(p, w, 0), n, stkD(p, w, 0), stkR(p, w, 0), n);
+    if (threadIdx.x == 0) p.logdet[w] = ld_;
+    cta_copy(p.G + (size_t)w * n * n, n, wk.b[1], wk.ld[1], n);
+}
+
+// Observables::calculate_{density,doubleOccupancy,swavePairing,densityCorr} (source/model.cpp:167-288)
+__global__ void __launch_bounds__(kThreads) k_measure(Params p, double* obs /*[W][4]*/, double* corr /*[W][N*N] or null*/) {
+    __shared__ double red[64];
+    const int w = blockIdx.x, n = p.N;
+    const double* G = p.G + (size_t)w * n * n;
+    double dsum = 0.0, d2sum = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const double gc = 1.0 - G[i + (size_t)i * n];
+        dsum += gc + gc;
+        d2sum += gc * gc;
+    }
+    dsum = cta_reduce_sum(dsum, red);
+    d2sum = cta_reduce_sum(d2sum, red);
+    double ssum = 0.0;
+    for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
+        const int j = e % n, i = e / n;
+        const double gc = ((i == j) ? 1.0 : 0.0) - G[j + (size_t)i * n];
+        ssum += gc * gc;
+    }
+    ssum = cta_reduce_sum(ssum, red);
+    const double navg = dsum / n;  // n_avg of calculate_densityCorr equals the density
+    if (threadIdx.x == 0) {
+        obs[w * 4 + 0] = dsum / n;
+        obs[w * 4 + 1] = d2sum / n;
+        obs[w * 4 + 2] = ssum / n;
+        obs[w * 4 + 3] = 0.0;
+    }
+    if (corr) {
+        double* C = corr + (size_t)w * n * n;
+        for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
+            const int i = e % n, j = e / n;
+            const double ni = 2.0 * (1.0 - G[i + (size_t)i * n]);
+            const double nj = 2.0 * (1.0 - G[j + (size_t)j * n]);
+            const double ex = 2.0 * (1.0 - G[j + (size_t)i * n]) * G[i + (size_t)j * n];  // Q5: 1.0, not delta_ij
+            C[i + (size_t)j * n] = ni * nj + ex - navg * navg;
+        }
+    }
+}
+
+// AttractiveHubbard::global_action (source/model.cpp:140-159)
+__global__ void __launch_bounds__(kThreads) k_action(Params p, double* S) {
+    __shared__ double red[64];
+    const int w = blockIdx.x;
+    const int8_t* f = p.fields + (size_t)w * p.nt * p.N;
+    double part = 0.0;
+    for (int e = threadIdx.x; e < p.nt * p.N; e += blockDim.x) part += p.lut_action[f[e]];
+    part = cta_reduce_sum(part, red);
+    if (threadIdx.x == 0) S[w] = -2.0 * p.logdet[w] - part;
+}
+
+// DQMC::half_warp, equal-time entry (source/dqmc.cpp:288-315)
+__global__ void __launch_bounds__(kThreads) k_half_wrap(Params p, double* out) {
+    const int w = blockIdx.x, n = p.N;
+    double* gws = p.ws + (size_t)w * 3 * n * p.LD;
+    cta_gemm<false>(gws, n, p.invexpK_half, 1, n, p.G + (size_t)w * n * n, 1, n, n, nullptr, nullptr);
+    __syncthreads();
+    cta_gemm<false>(out + (size_t)w * n * n, n, gws, 1, n, p.expK_half, 1, n, n, nullptr, nullptr);
+}
+
+// stand-alone batched stablelinalg ops on global buffers (ld = n).  op: 0 to_LDR, 1 mat_mul_ldr,
+// 2 ldr_mul_mat, 3 ldr_mul_ldr, 4 inv_I_plus_ldr, 5 inv_I_plus_ldr_mul_ldr
+struct LdrArgs {
+    const double *M, *L1, *d1, *R1, *L2, *d2, *R2;
+    double *Lo, *dO, *Ro, *G, *logdet;
+};
+__global__ void __launch_bounds__(kThreads) k_ldr_op(Params p, int op, LdrArgs a) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int w = blockIdx.x, n = p.N;
+    const size_t nn = (size_t)n * n;
+    Work wk;
+    carve(wk, p, w, p.smem_mats_stab, smem);
+    double *b0 = wk.b[0], *b1 = wk.b[1], *b2 = wk.b[2];
+    const int l0 = wk.ld[0], l1 = wk.ld[1], l2 = wk.ld[2];
+    const double* M = a.M ? a.M + w * nn : nullptr;
+    const double* L1 = a.L1 ? a.L1 + w * nn : nullptr;
+    const double* R1 = a.R1 ? a.R1 + w * nn : nullptr;
+    const double* d1 = a.d1 ? a.d1 + (size_t)w * n : nullptr;
+    const double* L2 = a.L2 ? a.L2 + w * nn : nullptr;
+    const double* R2 = a.R2 ? a.R2 + w * nn : nullptr;
+    const double* d2 = a.d2 ? a.d2 + (size_t)w * n : nullptr;
+    double* Lo = a.Lo ? a.Lo + w * nn : nullptr;
+    double* Ro = a.Ro ? a.Ro + w * nn : nullptr;
+    double* dO = a.dO ? a.dO + (size_t)w * n : nullptr;
+    double* G = a.G ? a.G + w * nn : nullptr;
+    if (op == 0) {
+        cta_copy(b0, l0, M, n, n);
+        dev_to_ldr(wk, n, b0, l0, b1, l1, b2, l2, wk.dnew);
+        cta_copy(Lo, n, b1, l1, n);
+        cta_copy(Ro, n, b2, l2, n);
+        store_d(dO, wk.dnew, n);
+    } else if (op == 1) {  // mat_mul_ldr(M, F1)
+        store_d(wk.sv[0], d1, n);
+        __syncthreads();
+        cta_gemm<false>(b1, l1, M, 1, n, L1, 1, n, n, nullptr, wk.sv[0]);
+        dev_to_ldr(wk, n, b1, l1, b0, l0, b2, l2, wk.dnew);
+        cta_gemm<false>(Ro, n, b2, 1, l2, R1, 1, n, n, nullptr, nullptr);
+        cta_copy(Lo, n, b0, l0, n);
+        store_d(dO, wk.dnew, n);
+    } else if (op == 2) {  // ldr_mul_mat(F1, M)
+        store_d(wk.sv[0], d1, n);
+        __syncthreads();
+        cta_gemm<false>(b1, l1, R1, 1, n, M, 1, n, n, wk.sv[0], nullptr);
+        dev_to_ldr(wk, n, b1, l1, b0, l0, b2, l2, wk.dnew);
+        cta_gemm<false>(Lo, n, L1, 1, n, b0, 1, l0, n, nullptr, nullptr);
+        cta_copy(Ro, n, b2, l2, n);
+        store_d(dO, wk.dnew, n);
+    } else if (op == 3) {  // ldr_mul_ldr(F1, F2)
+        store_d(wk.sv[0], d1, n);
+        store_d(wk.sv[2], d2, n);
+        __syncthreads();
+        cta_gemm<false>(b0, l0, R1, 1, n, L2, 1, n, n, wk.sv[0], wk.sv[2]);
+        dev_to_ldr(wk, n, b0, l0, b1, l1, b2, l2, wk.dnew);
+        cta_gemm<false>(Lo, n, L1, 1, n, b1, 1, l1, n, nullptr, nullptr);
+        cta_gemm<false>(Ro, n, b2, 1, l2, R2, 1, n, n, nullptr, nullptr);
+        store_d(dO, wk.dnew, n);
+    } else if (op == 4) {
+        const double ld_ = dev_inv_I_plus_ldr(p, wk, n, L1, n, d1, R1, n);
+        if (threadIdx.x == 0 && a.logdet) a.logdet[w] = ld_;
+        cta_copy(G, n, b1, l1, n);
+    } else if (op == 5) {
+        dev_inv_I_plus_ldr_mul_ldr(p, wk, n, L1, d1, R1, L2, d2, R2, n);
+        cta_copy(G, n, b2, l2, n);
+    }
+}
+
+// =====================================================================================================
+// host side
+// =====================================================================================================
+static thread_local std::string g_create_err;
+
+#define CK(call)                                                                                  \
+    do {                                                                                          \
+        cudaError_t e_ = (call);                                                                  \
+        if (e_ != cudaSuccess) {                                                                  \
+            ctx->err = std::string(#call) + ": " + cudaGetErrorString(e_);                        \
+            return DQMCB_ECUDA;                                                                   \
+        }                                                                                         \
+    } while (0)
+
+static size_t prop_small_bytes(int n) {
+    size_t off = (size_t)(5 * n) * 8 + (size_t)(3 * n) * 4 + (size_t)n;
+    return (off + 15) & ~(size_t)15;
+}
+
+static void fill_luts(const dqmcb_config& c, Params& p) {
+    for (int o = 0; o < 4; ++o) {
+        for (int nw = 0; nw < 4; ++nw) {
+            // AttractiveHubbard::bosonic_ratio / local_update_ratio (source/model.cpp:99-122)
+            const double d_eta = c.eta[nw] - c.eta[o];
+            const double boson = std::exp(c.alpha * c.g * d_eta);
+            const double delta = (1.0 / boson) - 1.0;
+            const double gammaR = c.gamma[nw] / c.gamma[o];
+            p.lut_delta[o * 4 + nw] = delta;
+            p.lut_gb[o * 4 + nw] = gammaR * boson;
+        }
+        p.lut_ev[o] = std::exp(c.g * c.eta[o]);   // source/model.cpp:69
+        p.lut_iev[o] = std::exp(-c.g * c.eta[o]);  // source/model.cpp:81
+        p.lut_action[o] = c.alpha * c.g * c.eta[o] + std::log(c.gamma[o]);
+    }
+}
+
+extern "C" {
+
+const char* dqmcb_version(void) { return "dqmc_b200 0.1 (sm_100a)"; }
+
+const char* dqmcb_last_error(const dqmcb_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+int dqmcb_partner_rank(int rank, int world_size, int exchange_attempt) {
+    // update::partner_rank (source/update.cpp:34-45): periodic even/odd pairing
+    const bool even_attempt = (exchange_attempt % 2 == 0);
+    const bool even_rank = (rank % 2 == 0);
+    const int off = (even_attempt == even_rank) ? 1 : -1;
+    return (rank + off + world_size) % world_size;
+}
+
+int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* invexpK, dqmcb_ctx** out) {
+    if (!cfg || !expK || !invexpK || !out) {
+        g_create_err = "null argument";
+        return DQMCB_EINVAL;
+    }
+    if (cfg->n_sites <= 0 || cfg->n_sites > 256 || cfg->nt <= 0 || cfg->n_stab <= 0 || cfg->n_walkers <= 0) {
+        g_create_err = "bad dimensions (need 0 < n_sites <= 256, nt > 0, n_stab > 0, n_walkers > 0)";
+        return DQMCB_EINVAL;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        g_create_err = "no CUDA device: dqmc_b200 has no CPU fallback";
+        return DQMCB_ECUDA;
+    }
+    if (cfg->device < 0 || cfg->device >= ndev) {
+        g_create_err = "bad device ordinal";
+        return DQMCB_EINVAL;
+    }
+    dqmcb_ctx* ctx = new dqmcb_ctx();
+    ctx->cfg = *cfg;
+    Params& p = ctx->p;
+    memset(&p, 0, sizeof(p));
+    const int N = cfg->n_sites, W = cfg->n_walkers, nt = cfg->nt;
+    p.N = N;
+    p.LD = (N % 2 == 0) ? N + 1 : N;  // odd leading dimension: conflict-free row access in SMEM
+    p.nt = nt;
+    p.n_stab = cfg->n_stab;
+    p.n_stack = (nt + cfg->n_stab - 1) / cfg->n_stab;
+    p.W = W;
+    p.rng_mode = DQMCB_RNG_PHILOX;
+    p.seed = 0x5DEECE66Dull;
+    fill_luts(*cfg, p);
+#define CKC(call)                                                          \
+    do {                                                                   \
+        cudaError_t e_ = (call);                                           \
+        if (e_ != cudaSuccess) {                                           \
+            g_create_err = std::string(#call) + ": " + cudaGetErrorString(e_); \
+            dqmcb_destroy(ctx);                                            \
+            return DQMCB_ECUDA;                                            \
+        }                                                                  \
+    } while (0)
+    CKC(cudaSetDevice(cfg->device));
+    const size_t nn = (size_t)N * N;
+    CKC(cudaMalloc(&ctx->d_expK, nn * 8));
+    CKC(cudaMalloc(&ctx->d_invexpK, nn * 8));
+    CKC(cudaMalloc(&ctx->d_expKh, nn * 8));
+    CKC(cudaMalloc(&ctx->d_invexpKh, nn * 8));
+    CKC(cudaMemcpy(ctx->d_expK, expK, nn * 8, cudaMemcpyHostToDevice));
+    CKC(cudaMemcpy(ctx->d_invexpK, invexpK, nn * 8, cudaMemcpyHostToDevice));
+    CKC(cudaMemset(ctx->d_expKh, 0, nn * 8));
+    CKC(cudaMemset(ctx->d_invexpKh, 0, nn * 8));
+    p.expK = ctx->d_expK;
+    p.invexpK = ctx->d_invexpK;
+    p.expK_half = ctx->d_expKh;
+    p.invexpK_half = ctx->d_invexpKh;
+    CKC(cudaMalloc(&p.fields, (size_t)W * nt * N));
+    CKC(cudaMemset(p.fields, 0, (size_t)W * nt * N));
+    CKC(cudaMalloc(&p.G, W * nn * 8));
+    CKC(cudaMalloc(&p.Bbar, W * nn * 8));
+    CKC(cudaMalloc(&p.stackL, (size_t)W * p.n_stack * nn * 8));
+    CKC(cudaMalloc(&p.stackR, (size_t)W * p.n_stack * nn * 8));
+    CKC(cudaMalloc(&p.stackD, (size_t)W * p.n_stack * N * 8));
+    CKC(cudaMalloc(&p.ws, (size_t)W * 3 * N * p.LD * 8));
+    CKC(cudaMalloc(&p.logdet, (size_t)W * 8));
+    CKC(cudaMalloc(&p.accepted, (size_t)W * 8));
+    CKC(cudaMalloc(&p.err_max, (size_t)W * 8));
+    CKC(cudaMalloc(&p.err_sum, (size_t)W * 8));
+    CKC(cudaMalloc(&p.err_cnt, (size_t)W * 8));
+    CKC(cudaMalloc(&p.fail, sizeof(int)));
+    CKC(cudaMalloc(&ctx->d_obs, (size_t)W * 4 * 8));
+    CKC(cudaMalloc(&ctx->d_scratchNN, W * nn * 8));
+    CKC(cudaMemset(p.G, 0, W * nn * 8));
+    CKC(cudaMemset(p.logdet, 0, (size_t)W * 8));
+    CKC(cudaMemset(p.accepted, 0, (size_t)W * 8));
+    CKC(cudaMemset(p.err_max, 0, (size_t)W * 8));
+    CKC(cudaMemset(p.err_sum, 0, (size_t)W * 8));
+    CKC(cudaMemset(p.err_cnt, 0, (size_t)W * 8));
+    CKC(cudaMemset(p.fail, 0, sizeof(int)));
+    // shared-memory plan
+    const size_t tile = (size_t)N * p.LD * 8;
+    const size_t sb = ((small_bytes(N) + 15) & ~(size_t)15);
+    p.smem_mats_stab = (sb + 3 * tile <= (size_t)kMaxSmem) ? 3 : 0;
+    ctx->smem_stab = sb + p.smem_mats_stab * tile;
+    const size_t pb = prop_small_bytes(N);
+    p.smem_mats_prop = (pb + 2 * tile <= (size_t)kMaxSmem) ? 2 : ((pb + tile <= (size_t)kMaxSmem) ? 1 : 0);
+    ctx->smem_prop = pb + p.smem_mats_prop * tile;
+    CKC(cudaFuncSetAttribute(k_propagate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_prop));
+    CKC(cudaFuncSetAttribute(k_bbar, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
+    CKC(cudaFuncSetAttribute(k_stabilize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
+    CKC(cudaFuncSetAttribute(k_init_stacks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
+    CKC(cudaFuncSetAttribute(k_init_green, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
+    CKC(cudaFuncSetAttribute(k_ldr_op, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
+    CKC(fast64_setup(ctx));
+#undef CKC
+    *out = ctx;
+    return DQMCB_OK;
+}
+
+void dqmcb_destroy(dqmcb_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->cfg.device);
+    Params& p = ctx->p;
+    cudaFree(ctx->d_expK);
+    cudaFree(ctx->d_invexpK);
+    cudaFree(ctx->d_expKh);
+    cudaFree(ctx->d_invexpKh);
+    cudaFree(p.fields);
+    cudaFree(p.G);
+    cudaFree(p.Bbar);
+    cudaFree(p.stackL);
+    cudaFree(p.stackR);
+    cudaFree(p.stackD);
+    cudaFree(p.ws);
+    cudaFree(p.logdet);
+    cudaFree(p.accepted);
+    cudaFree(p.err_max);
+    cudaFree(p.err_sum);
+    cudaFree(p.err_cnt);
+    cudaFree(p.fail);
+    cudaFree(ctx->d_obs);
+    cudaFree(ctx->d_scratchNN);
+    cudaFree(ctx->d_tape_perm);
+    cudaFree(ctx->d_tape_k);
+    cudaFree(ctx->d_tape_u);
+    cudaFree(ctx->d_mt);
+    delete ctx;
+}
+
+#define NEED(ctx)                     \
+    if (!(ctx)) return DQMCB_EINVAL;  \
+    CK(cudaSetDevice((ctx)->cfg.device))
+
+int dqmcb_set_stream(dqmcb_ctx* ctx, void* s) {
+    if (!ctx) return DQMCB_EINVAL;
+    ctx->stream = (cudaStream_t)s;
+    return DQMCB_OK;
+}
+int dqmcb_synchronize(dqmcb_ctx* ctx) {
+    NEED(ctx);
+    CK(cudaStreamSynchronize(ctx->stream));
+    int fail = 0;
+    CK(cudaMemcpy(&fail, ctx->p.fail, sizeof(int), cudaMemcpyDeviceToHost));
+    if (fail) {
+        ctx->err = "LU factorisation hit an exactly singular pivot (code " + std::to_string(fail) + ")";
+        cudaMemset(ctx->p.fail, 0, sizeof(int));
+        return DQMCB_ENUMERIC;
+    }
+    return DQMCB_OK;
+}
+int dqmcb_n_stack(const dqmcb_ctx* ctx) { return ctx ? ctx->p.n_stack : -1; }
+
+int dqmcb_set_half_expK(dqmcb_ctx* ctx, const double* a, const double* b) {
+    NEED(ctx);
+    const size_t nn = (size_t)ctx->p.N * ctx->p.N;
+    CK(cudaMemcpy(ctx->d_expKh, a, nn * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ctx->d_invexpKh, b, nn * 8, cudaMemcpyHostToDevice));
+    return DQMCB_OK;
+}
+
+// ---- fields -----------------------------------------------------------------------------------------
+int dqmcb_set_fields(dqmcb_ctx* ctx, const int8_t* f) {
+    NEED(ctx);
+    const size_t sz = (size_t)ctx->p.W * ctx->p.nt * ctx->p.N;
+    for (size_t i = 0; i < sz; ++i)
+        if (f[i] < 0 || f[i] > 3) {
+            ctx->err = "field value outside {0,1,2,3}";
+            return DQMCB_EINVAL;
+        }
+    CK(cudaMemcpyAsync(ctx->p.fields, f, sz, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->stacks_ready = ctx->green_ready = false;
+    return DQMCB_OK;
+}
+int dqmcb_get_fields(dqmcb_ctx* ctx, int8_t* f) {
+    NEED(ctx);
+    const size_t sz = (size_t)ctx->p.W * ctx->p.nt * ctx->p.N;
+    CK(cudaMemcpyAsync(f, ctx->p.fields, sz, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DQMCB_OK;
+}
+int dqmcb_set_fields_i64(dqmcb_ctx* ctx, int walker, const long long* f) {
+    NEED(ctx);
+    const int nt = ctx->p.nt, N = ctx->p.N;
+    if (walker < 0 || walker >= ctx->p.W) return DQMCB_EINVAL;
+    std::vector<int8_t> tmp((size_t)nt * N);
+    for (int s = 0; s < N; ++s)
+        for (int l = 0; l < nt; ++l) {
+            const long long v = f[l + (size_t)s * nt];  // arma::imat(nt, N) column-major
+            if (v < 0 || v > 3) {
+                ctx->err = "field value outside {0,1,2,3}";
+                return DQMCB_EINVAL;
+            }
+            tmp[(size_t)l * N + s] = (int8_t)v;
+        }
+    CK(cudaMemcpy(ctx->p.fields + (size_t)walker * nt * N, tmp.data(), tmp.size(), cudaMemcpyHostToDevice));
+    ctx->stacks_ready = ctx->green_ready = false;
+    return DQMCB_OK;
+}
+int dqmcb_get_fields_i64(dqmcb_ctx* ctx, int walker, long long* f) {
+    NEED(ctx);
+    const int nt = ctx->p.nt, N = ctx->p.N;
+    if (walker < 0 || walker >= ctx->p.W) return DQMCB_EINVAL;
+    std::vector<int8_t> tmp((size_t)nt * N);
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(tmp.data(), ctx->p.fields + (size_t)walker * nt * N, tmp.size(), cudaMemcpyDeviceToHost));
+    for (int s = 0; s < N; ++s)
+        for (int l = 0; l < nt; ++l) f[l + (size_t)s * nt] = tmp[(size_t)l * N + s];
+    return DQMCB_OK;
+}
+
+// ---- RNG ----------------------------------------------------------------------------------------------
+int dqmcb_rng_mode(dqmcb_ctx* ctx, int mode, uint64_t seed) {
+    if (!ctx) return DQMCB_EINVAL;
+    if (mode != DQMCB_RNG_TAPE && mode != DQMCB_RNG_PHILOX && mode != DQMCB_RNG_MT19937) return DQMCB_EINVAL;
+    if (mode == DQMCB_RNG_MT19937) {
+        ctx->err = "device mt19937 stream not built in this version: replay it through DQMCB_RNG_TAPE";
+        return DQMCB_EINVAL;
+    }
+    ctx->p.rng_mode = mode;
+    ctx->p.seed = seed;
+    ctx->p.visit_base = 0;
+    ctx->tape_pos = 0;
+    ctx->p.tape_visits = 0;
+    return DQMCB_OK;
+}
+int dqmcb_rng_seed_mt19937(dqmcb_ctx* ctx, const uint32_t*) {
+    if (!ctx) return DQMCB_EINVAL;
+    ctx->err = "device mt19937 stream not built in this version: replay it through DQMCB_RNG_TAPE";
+    return DQMCB_EINVAL;
+}
+int dqmcb_set_tape(dqmcb_ctx* ctx, int n_visits, const uint8_t* perm, const uint8_t* knew, const double* u) {
+    NEED(ctx);
+    if (n_visits <= 0 || !perm || !knew || !u) return DQMCB_EINVAL;
+    const size_t cnt = (size_t)ctx->p.W * n_visits * ctx->p.N;
+    CK(cudaStreamSynchronize(ctx->stream));
+    if ((size_t)n_visits > ctx->tape_cap) {
+        cudaFree(ctx->d_tape_perm);
+        cudaFree(ctx->d_tape_k);
+        cudaFree(ctx->d_tape_u);
+        CK(cudaMalloc(&ctx->d_tape_perm, cnt));
+        CK(cudaMalloc(&ctx->d_tape_k, cnt));
+        CK(cudaMalloc(&ctx->d_tape_u, cnt * 8));
+        ctx->tape_cap = n_visits;
+    }
+    CK(cudaMemcpy(ctx->d_tape_perm, perm, cnt, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ctx->d_tape_k, knew, cnt, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(ctx->d_tape_u, u, cnt * 8, cudaMemcpyHostToDevice));
+    ctx->p.tape_perm = ctx->d_tape_perm;
+    ctx->p.tape_k = ctx->d_tape_k;
+    ctx->p.tape_u = ctx->d_tape_u;
+    ctx->p.tape_visits = n_visits;
+    ctx->p.rng_mode = DQMCB_RNG_TAPE;
+    ctx->tape_pos = 0;
+    ctx->p.visit_base = 0;
+    return DQMCB_OK;
+}
+
+// consume `n` visits: returns the first visit index to hand to the kernel
+static int take_visits(dqmcb_ctx* ctx, int n, unsigned long long* first) {
+    if (ctx->p.rng_mode == DQMCB_RNG_TAPE) {
+        if (ctx->tape_pos + n > ctx->p.tape_visits) {
+            ctx->err = "RNG tape exhausted: call dqmcb_set_tape with enough visits";
+            return DQMCB_ESTATE;
+        }
+        *first = (unsigned long long)ctx->tape_pos;
+        ctx->tape_pos += n;
+    } else {
+        *first = ctx->p.visit_base;
+        ctx->p.visit_base += n;
+    }
+    return DQMCB_OK;
+}
+
+// ---- launches -------------------------------------------------------------------------------------------
+static int launch_propagate(dqmcb_ctx* ctx, int l_first, int n_slices, int dir, int flags) {
+    unsigned long long v0 = 0;
+    if (flags & 2) {
+        int rc = take_visits(ctx, n_slices, &v0);
+        if (rc) return rc;
+    }
+    Params p = ctx->p;
+    if (p.rng_mode != DQMCB_RNG_TAPE) p.visit_base = 0;
+    if (fast64_available(ctx)) return fast64_propagate(ctx, p, l_first, n_slices, dir, v0, flags);
+    k_propagate<<<p.W, kThreads, ctx->smem_prop, ctx->stream>>>(p, l_first, n_slices, dir, v0, flags);
+    CK(cudaGetLastError());
+    return DQMCB_OK;
+}
+
+int dqmcb_init_stacks(dqmcb_ctx* ctx) {
+    NEED(ctx);
+    k_init_stacks<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p);
+    CK(cudaGetLastError());
+    ctx->stacks_ready = true;
+    return DQMCB_OK;
+}
+int dqmcb_init_greenfunctions(dqmcb_ctx* ctx) {
+    NEED(ctx);
+    if (!ctx->stacks_ready) {
+        ctx->err = "init_greenfunctions before init_stacks";
+        return DQMCB_ESTATE;
+    }
+    k_init_green<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p);
+    CK(cudaGetLastError());
+    ctx->green_ready = true;
+    return DQMCB_OK;
+}
+static int check_l(dqmcb_ctx* ctx, int l) {
+    if (l < 0 || l >= ctx->p.nt) {
+        ctx->err = "time slice out of range";
+        return DQMCB_EINVAL;
+    }
+    return DQMCB_OK;
+}
+int dqmcb_wrap_forward(dqmcb_ctx* ctx, int l) {
+    NEED(ctx);
+    if (int rc = check_l(ctx, l)) return rc;
+    return launch_propagate(ctx, l, 1, +1, 1);
+}
+int dqmcb_wrap_backward(dqmcb_ctx* ctx, int l) {
+    NEED(ctx);
+    if (int rc = check_l(ctx, l)) return rc;
+    return launch_propagate(ctx, l, 1, -1, 1);
+}
+int dqmcb_local_update(dqmcb_ctx* ctx, int l) {
+    NEED(ctx);
+    if (int rc = check_l(ctx, l)) return rc;
+    return launch_propagate(ctx, l, 1, +1, 2);
+}
+int dqmcb_block_product(dqmcb_ctx* ctx, int i_stack) {
+    NEED(ctx);
+    if (i_stack < 0 || i_stack >= ctx->p.n_stack) {
+        ctx->err = "LDR Stack index out of bounds";
+        return DQMCB_EINVAL;
+    }
+    k_bbar<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p, i_stack);
+    CK(cudaGetLastError());
+    return DQMCB_OK;
+}
+int dqmcb_get_block_product(dqmcb_ctx* ctx, double* out) {
+    NEED(ctx);
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(out, ctx->p.Bbar, (size_t)ctx->p.W * ctx->p.N * ctx->p.N * 8, cudaMemcpyDeviceToHost));
+    return DQMCB_OK;
+}
+static int launch_stabilize(dqmcb_ctx* ctx, int l, int dir) {
+    k_stabilize<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p, l, dir);
+    CK(cudaGetLastError());
+    return DQMCB_OK;
+}
+int dqmcb_stabilize_forward(dqmcb_ctx* ctx, int l) {
+    NEED(ctx);
+    if (int rc = check_l(ctx, l)) return rc;
+    return launch_stabilize(ctx, l, +1);
+}
+int dqmcb_stabilize_backward(dqmcb_ctx* ctx, int l) {
+    NEED(ctx);
+    if (int rc = check_l(ctx, l)) return rc;
+    return launch_stabilize(ctx, l, -1);
+}
+
+int dqmcb_sweep_0_to_beta(dqmcb_ctx* ctx) {
+    NEED(ctx);
+    if (!ctx->green_ready) {
+        ctx->err = "sweep before init_stacks/init_greenfunctions";
+        return DQMCB_ESTATE;
+    }
+    const Params& p = ctx->p;
+    for (int i = 0; i < p.n_stack; ++i) {
+        const int l0 = i * p.n_stab, l1 = std::min(l0 + p.n_stab, p.nt);
+        if (int rc = launch_propagate(ctx, l0, l1 - l0, +1, 3)) return rc;
+        if (int rc = launch_stabilize(ctx, l1 - 1, +1)) return rc;
+    }
+    return DQMCB_OK;
+}
+int dqmcb_sweep_beta_to_0(dqmcb_ctx* ctx) {
+    NEED(ctx);
+    if (!ctx->green_ready) {
+        ctx->err = "sweep before init_stacks/init_greenfunctions";
+        return DQMCB_ESTATE;
+    }
+    const Params& p = ctx->p;
+    for (int i = p.n_stack - 1; i >= 0; --i) {
+        const int l0 = i * p.n_stab, l1 = std::min(l0 + p.n_stab, p.nt);
+        if (int rc = launch_propagate(ctx, l1 - 1, l1 - l0, -1, 3)) return rc;
+        if (int rc = launch_stabilize(ctx, l0, -1)) return rc;
+    }
+    return DQMCB_OK;
+}
+
+// ---- state access -------------------------------------------------------------------------------------------
+int dqmcb_get_G(dqmcb_ctx* ctx, double* G) {
+    NEED(ctx);
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(G, ctx->p.G, (size_t)ctx->p.W * ctx->p.N * ctx->p.N * 8, cudaMemcpyDeviceToHost));
+    return dqmcb_synchronize(ctx);
+}
+int dqmcb_set_G(dqmcb_ctx* ctx, const double* G) {
+    NEED(ctx);
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(ctx->p.G, G, (size_t)ctx->p.W * ctx->p.N * ctx->p.N * 8, cudaMemcpyHostToDevice));
+    ctx->green_ready = true;
+    return DQMCB_OK;
+}
+int dqmcb_get_ldr(dqmcb_ctx* ctx, int i, double* L, double* d, double* R) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    if (i < 0 || i >= p.n_stack) {
+        ctx->err = "LDR Stack index out of bounds";
+        return DQMCB_EINVAL;
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    const size_t nn = (size_t)p.N * p.N;
+    for (int w = 0; w < p.W; ++w) {
+        const size_t so = (size_t)w * p.n_stack + i;
+        if (L) CK(cudaMemcpy(L + w * nn, p.stackL + so * nn, nn * 8, cudaMemcpyDeviceToHost));
+        if (R) CK(cudaMemcpy(R + w * nn, p.stackR + so * nn, nn * 8, cudaMemcpyDeviceToHost));
+        if (d) CK(cudaMemcpy(d + (size_t)w * p.N, p.stackD + so * p.N, (size_t)p.N * 8, cudaMemcpyDeviceToHost));
+    }
+    return dqmcb_synchronize(ctx);
+}
+int dqmcb_set_ldr(dqmcb_ctx* ctx, int i, const double* L, const double* d, const double* R) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    if (i < 0 || i >= p.n_stack) {
+        ctx->err = "LDR Stack index out of bounds";
+        return DQMCB_EINVAL;
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    const size_t nn = (size_t)p.N * p.N;
+    for (int w = 0; w < p.W; ++w) {
+        const size_t so = (size_t)w * p.n_stack + i;
+        CK(cudaMemcpy(p.stackL + so * nn, L + w * nn, nn * 8, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(p.stackR + so * nn, R + w * nn, nn * 8, cudaMemcpyHostToDevice));
+        CK(cudaMemcpy(p.stackD + so * p.N, d + (size_t)w * p.N, (size_t)p.N * 8, cudaMemcpyHostToDevice));
+    }
+    ctx->stacks_ready = true;
+    return DQMCB_OK;
+}
+int dqmcb_get_logdet(dqmcb_ctx* ctx, double* out) {
+    NEED(ctx);
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(out, ctx->p.logdet, (size_t)ctx->p.W * 8, cudaMemcpyDeviceToHost));
+    return DQMCB_OK;
+}
+int dqmcb_get_stats(dqmcb_ctx* ctx, double* acc_rate, double* max_err, double* mean_err) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    CK(cudaStreamSynchronize(ctx->stream));
+    std::vector<unsigned long long> acc(p.W), cnt(p.W);
+    std::vector<double> emax(p.W), esum(p.W);
+    CK(cudaMemcpy(acc.data(), p.accepted, (size_t)p.W * 8, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(cnt.data(), p.err_cnt, (size_t)p.W * 8, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(emax.data(), p.err_max, (size_t)p.W * 8, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(esum.data(), p.err_sum, (size_t)p.W * 8, cudaMemcpyDeviceToHost));
+    for (int w = 0; w < p.W; ++w) {
+        // acc_rate_ accumulates accepted/N/nt per slice (source/dqmc.cpp:366, update.cpp:31)
+        if (acc_rate) acc_rate[w] = (double)acc[w] / ((double)p.N * (double)p.nt);
+        if (max_err) max_err[w] = emax[w];
+        if (mean_err) mean_err[w] = cnt[w] ? esum[w] / (double)cnt[w] : 0.0;
+    }
+    return DQMCB_OK;
+}
+int dqmcb_reset_stats(dqmcb_ctx* ctx) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    CK(cudaMemsetAsync(p.accepted, 0, (size_t)p.W * 8, ctx->stream));
+    CK(cudaMemsetAsync(p.err_max, 0, (size_t)p.W * 8, ctx->stream));
+    CK(cudaMemsetAsync(p.err_sum, 0, (size_t)p.W * 8, ctx->stream));
+    CK(cudaMemsetAsync(p.err_cnt, 0, (size_t)p.W * 8, ctx->stream));
+    return DQMCB_OK;
+}
+void* dqmcb_device_ptr(dqmcb_ctx* ctx, int which) {
+    if (!ctx) return nullptr;
+    switch (which) {
+        case DQMCB_PTR_FIELDS: return ctx->p.fields;
+        case DQMCB_PTR_G: return ctx->p.G;
+        case DQMCB_PTR_LOGDET: return ctx->p.logdet;
+        case DQMCB_PTR_OBS: return ctx->d_obs;
+        default: return nullptr;
+    }
+}
+
+// ---- measurements ------------------------------------------------------------------------------------------------
+int dqmcb_measure_equal_time(dqmcb_ctx* ctx, double* scalars, double* corr) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    k_measure<<<p.W, kThreads, 0, ctx->stream>>>(p, ctx->d_obs, corr ? ctx->d_scratchNN : nullptr);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(ctx->stream));
+    std::vector<double> o((size_t)p.W * 4);
+    CK(cudaMemcpy(o.data(), ctx->d_obs, o.size() * 8, cudaMemcpyDeviceToHost));
+    if (scalars)
+        for (int w = 0; w < p.W; ++w)
+            for (int k = 0; k < 3; ++k) scalars[w * 3 + k] = o[w * 4 + k];
+    if (corr) CK(cudaMemcpy(corr, ctx->d_scratchNN, (size_t)p.W * p.N * p.N * 8, cudaMemcpyDeviceToHost));
+    return DQMCB_OK;
+}
+int dqmcb_global_action(dqmcb_ctx* ctx, double* S) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    k_action<<<p.W, kThreads, 0, ctx->stream>>>(p, ctx->d_obs);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(S, ctx->d_obs, (size_t)p.W * 8, cudaMemcpyDeviceToHost));
+    return DQMCB_OK;
+}
+int dqmcb_half_wrap(dqmcb_ctx* ctx, double* Gsym) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    k_half_wrap<<<p.W, kThreads, 0, ctx->stream>>>(p, ctx->d_scratchNN);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(Gsym, ctx->d_scratchNN, (size_t)p.W * p.N * p.N * 8, cudaMemcpyDeviceToHost));
+    return DQMCB_OK;
+}
+
+int dqmcb_run_sweeps_host(dqmcb_ctx* ctx, int reinit, const int8_t* fields_in, int n_sweeps, int8_t* fields_out, double* scalars_out,
+                          double* G_out) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    const size_t fsz = (size_t)p.W * p.nt * p.N;
+    if (fields_in) {
+        CK(cudaMemcpyAsync(p.fields, fields_in, fsz, cudaMemcpyHostToDevice, ctx->stream));
+        ctx->stacks_ready = ctx->green_ready = false;
+    }
+    if (reinit || !ctx->green_ready) {
+        if (int rc = dqmcb_init_stacks(ctx)) return rc;
+        if (int rc = dqmcb_init_greenfunctions(ctx)) return rc;
+    }
+    for (int s = 0; s < n_sweeps; ++s) {
+        if (int rc = dqmcb_sweep_0_to_beta(ctx)) return rc;
+        if (int rc = dqmcb_sweep_beta_to_0(ctx)) return rc;
+    }
+    if (scalars_out) {
+        k_measure<<<p.W, kThreads, 0, ctx->stream>>>(p, ctx->d_obs, nullptr);
+        CK(cudaGetLastError());
+    }
+    if (fields_out) CK(cudaMemcpyAsync(fields_out, p.fields, fsz, cudaMemcpyDeviceToHost, ctx->stream));
+    if (G_out) CK(cudaMemcpyAsync(G_out, p.G, (size_t)p.W * p.N * p.N * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (scalars_out) {
+        // d_obs rows are [density, doubleOcc, swave, pad]; copy as W x 4 then compact on the host
+        std::vector<double> o((size_t)p.W * 4);
+        CK(cudaMemcpyAsync(o.data(), ctx->d_obs, o.size() * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        for (int w = 0; w < p.W; ++w)
+            for (int k = 0; k < 3; ++k) scalars_out[w * 3 + k] = o[w * 4 + k];
+    }
+    return dqmcb_synchronize(ctx);
+}
+
+// ---- stand-alone batched stablelinalg ---------------------------------------------------------------------------
+static int run_ldr_op(int device, int n, int batch, int op, const double* M, const double* L1, const double* d1, const double* R1,
+                      const double* L2, const double* d2, const double* R2, double* Lo, double* dO, double* Ro, double* G,
+                      double* logdet) {
+    if (n <= 0 || n > 256 || batch <= 0) return DQMCB_EINVAL;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        g_create_err = "no CUDA device: dqmc_b200 has no CPU fallback";
+        return DQMCB_ECUDA;
+    }
+    if (cudaSetDevice(device) != cudaSuccess) return DQMCB_ECUDA;
+    Params p;
+    memset(&p, 0, sizeof(p));
+    p.N = n;
+    p.LD = (n % 2 == 0) ? n + 1 : n;
+    p.W = batch;
+    const size_t nn = (size_t)n * n, tile = (size_t)n * p.LD * 8;
+    const size_t sb = ((small_bytes(n) + 15) & ~(size_t)15);
+    p.smem_mats_stab = (sb + 3 * tile <= (size_t)kMaxSmem) ? 3 : 0;
+    const size_t smem = sb + p.smem_mats_stab * tile;
+    std::vector<void*> allocs;
+    int rc = DQMCB_OK;
+    auto up = [&](const double* h, size_t cnt) -> double* {
+        if (!h) return nullptr;
+        double* dptr = nullptr;
+        if (cudaMalloc(&dptr, cnt * 8) != cudaSuccess) {
+            rc = DQMCB_ECUDA;
+            return nullptr;
+        }
+        allocs.push_back(dptr);
+        if (cudaMemcpy(dptr, h, cnt * 8, cudaMemcpyHostToDevice) != cudaSuccess) rc = DQMCB_ECUDA;
+        return dptr;
+    };
+    auto mk = [&](bool want, size_t cnt) -> double* {
+        if (!want) return nullptr;
+        double* dptr = nullptr;
+        if (cudaMalloc(&dptr, cnt * 8) != cudaSuccess) {
+            rc = DQMCB_ECUDA;
+            return nullptr;
+        }
+        allocs.push_back(dptr);
+        return dptr;
+    };
+    LdrArgs a;
+    a.M = up(M, batch * nn);
+    a.L1 = up(L1, batch * nn);
+    a.d1 = up(d1, (size_t)batch * n);
+    a.R1 = up(R1, batch * nn);
+    a.L2 = up(L2, batch * nn);
+    a.d2 = up(d2, (size_t)batch * n);
+    a.R2 = up(R2, batch * nn);
+    a.Lo = mk(Lo, batch * nn);
+    a.dO = mk(dO, (size_t)batch * n);
+    a.Ro = mk(Ro, batch * nn);
+    a.G = mk(G, batch * nn);
+    a.logdet = mk(logdet, batch);
+    p.ws = mk(true, (size_t)batch * 3 * n * p.LD);
+    int* fail = nullptr;
+    if (cudaMalloc(&fail, sizeof(int)) != cudaSuccess) rc = DQMCB_ECUDA;
+    if (rc == DQMCB_OK) {
+        cudaMemset(fail, 0, sizeof(int));
+        p.fail = fail;
+        cudaFuncSetAttribute(k_ldr_op, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        k_ldr_op<<<batch, kThreads, smem>>>(p, op, a);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) {
+            g_create_err = cudaGetErrorString(e);
+            rc = DQMCB_ECUDA;
+        }
+    }
+    if (rc == DQMCB_OK) {
+        int f = 0;
+        cudaMemcpy(&f, fail, sizeof(int), cudaMemcpyDeviceToHost);
+        if (f) rc = DQMCB_ENUMERIC;
+        if (Lo) cudaMemcpy(Lo, a.Lo, batch * nn * 8, cudaMemcpyDeviceToHost);
+        if (dO) cudaMemcpy(dO, a.dO, (size_t)batch * n * 8, cudaMemcpyDeviceToHost);
+        if (Ro) cudaMemcpy(Ro, a.Ro, batch * nn * 8, cudaMemcpyDeviceToHost);
+        if (G) cudaMemcpy(G, a.G, batch * nn * 8, cudaMemcpyDeviceToHost);
+        if (logdet) cudaMemcpy(logdet, a.logdet, (size_t)batch * 8, cudaMemcpyDeviceToHost);
+    }
+    for (void* q : allocs) cudaFree(q);
+    cudaFree(fail);
+    return rc;
+}
+
+int dqmcb_to_LDR(int device, int n, int batch, const double* M, double* L, double* d, double* R) {
+    return run_ldr_op(device, n, batch, 0, M, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, L, d, R, nullptr, nullptr);
+}
+int dqmcb_mat_mul_ldr(int device, int n, int batch, const double* M, const double* L, const double* d, const double* R, double* Lo,
+                      double* dO, double* Ro) {
+    return run_ldr_op(device, n, batch, 1, M, L, d, R, nullptr, nullptr, nullptr, Lo, dO, Ro, nullptr, nullptr);
+}
+int dqmcb_ldr_mul_mat(int device, int n, int batch, const double* L, const double* d, const double* R, const double* M, double* Lo,
+                      double* dO, double* Ro) {
+    return run_ldr_op(device, n, batch, 2, M, L, d, R, nullptr, nullptr, nullptr, Lo, dO, Ro, nullptr, nullptr);
+}
+int dqmcb_ldr_mul_ldr(int device, int n, int batch, const double* L1, const double* d1, const double* R1, const double* L2,
+                      const double* d2, const double* R2, double* Lo, double* dO, double* Ro) {
+    return run_ldr_op(device, n, batch, 3, nullptr, L1, d1, R1, L2, d2, R2, Lo, dO, Ro, nullptr, nullptr);
+}
+int dqmcb_inv_I_plus_ldr(int device, int n, int batch, const double* L, const double* d, const double* R, double* G, double* logdet) {
+    return run_ldr_op(device, n, batch, 4, nullptr, L, d, R, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, G, logdet);
+}
+int dqmcb_inv_I_plus_ldr_mul_ldr(int device, int n, int batch, const double* L1, const double* d1, const double* R1, const double* L2,
+                                 const double* d2, const double* R2, double* G) {
+    return run_ldr_op(device, n, batch, 5, nullptr, L1, d1, R1, L2, d2, R2, nullptr, nullptr, nullptr, G, nullptr);
+}
+
+}  // extern "C"

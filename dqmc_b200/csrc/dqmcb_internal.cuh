@@ -1,0 +1,72 @@
+// dqmcb_internal.cuh -- shared declarations of the sweep engine (device parameter block, context).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+
+#include "../../include/dqmc_b200.h"
+
+namespace dq {
+
+constexpr int kThreads = 256;        // threads per CTA of the generic kernels
+constexpr int kMaxSmem = 227 * 1024; // opt-in dynamic shared memory per CTA on sm_100a
+
+// Everything a kernel needs; passed by value (lives in constant bank / param space).
+struct Params {
+    int N, LD, nt, n_stab, n_stack, W;
+    int smem_mats_prop;  // how many N x LD matrices of the propagate kernel live in SMEM (0..2)
+    int smem_mats_stab;  // ... of the stabilisation kernels (0 or 3)
+    const double* expK;
+    const double* invexpK;
+    const double* expK_half;
+    const double* invexpK_half;
+    int8_t* fields;   // [W][nt][N]
+    double* G;        // [W][N*N]   current equal-time Green's function, column-major, ld = N
+    double* Bbar;     // [W][N*N]
+    double* stackL;   // [W][n_stack][N*N]
+    double* stackD;   // [W][n_stack][N]
+    double* stackR;   // [W][n_stack][N*N]
+    double* ws;       // [W][3][N*LD]  global workspace when the tiles do not fit in SMEM
+    double* logdet;   // [W]
+    // RNG
+    int rng_mode;
+    uint64_t seed;
+    unsigned long long visit_base;  // visits (local_update calls) consumed so far
+    const uint8_t* tape_perm;       // [W][tape_visits][N]
+    const uint8_t* tape_k;
+    const double* tape_u;
+    int tape_visits;
+    // statistics
+    unsigned long long* accepted;  // [W]
+    double* err_max;               // [W]
+    double* err_sum;               // [W]
+    unsigned long long* err_cnt;   // [W]
+    int* fail;                     // [1] first failing info code
+    // lookup tables (flip ratio / B-matrix diagonals), computed on the host with the reference's formulas
+    double lut_delta[16];  // [old*4+new]  exp(g d_eta) - 1       source/model.cpp:103-105
+    double lut_gb[16];     // [old*4+new]  gammaR * bosonR       source/model.cpp:117,121
+    double lut_ev[4];      // exp(+g eta)                         source/model.cpp:69
+    double lut_iev[4];     // exp(-g eta)                         source/model.cpp:81
+    double lut_action[4];  // alpha g eta(s) + log gamma(s)       source/model.cpp:153-154
+};
+
+}  // namespace dq
+
+struct dqmcb_ctx {
+    dqmcb_config cfg;
+    dq::Params p;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    bool stacks_ready = false, green_ready = false;
+    // owned device allocations
+    double *d_expK = nullptr, *d_invexpK = nullptr, *d_expKh = nullptr, *d_invexpKh = nullptr;
+    uint8_t *d_tape_perm = nullptr, *d_tape_k = nullptr;
+    double* d_tape_u = nullptr;
+    size_t tape_cap = 0;  // visits allocated
+    int tape_pos = 0;     // next visit to consume (TAPE mode)
+    double* d_obs = nullptr;  // [W][4]
+    double* d_scratchNN = nullptr;  // [W][N*N] for measurement outputs
+    uint32_t* d_mt = nullptr;       // [W][625] mt19937 state + index (MT19937 mode)
+    size_t smem_prop = 0, smem_stab = 0;
+};

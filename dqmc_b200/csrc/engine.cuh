@@ -1,0 +1,361 @@
+// engine.cuh -- generic-N device code of the sweep engine (one CTA per walker).
+//
+// Device restatement of the reference's equal-time sweep (source/dqmc.cpp, source/update.cpp,
+// source/model.cpp, source/stablelinalg.cpp) on top of the CTA-level primitives in linalg.cuh.
+// Works for any N; tiles live in shared memory when they fit, otherwise in an L2-resident
+// global workspace.  The N = 64 fast path (DMMA wrap, register-resident flips) lives in
+// fast64.cuh and is parity-tested against this path as well as against the oracle.
+#pragma once
+#include "dqmcb_internal.cuh"
+#include "linalg.cuh"
+
+namespace dq {
+
+// --------------------------------------------------------------------------------------------------
+// per-CTA workspace carved out of dynamic shared memory (+ global fallback for the big tiles)
+// --------------------------------------------------------------------------------------------------
+struct Work {
+    double* b[3];  // N x LD tiles
+    int ld[3];
+    double *tau, *vn1, *vn2, *sv[4], *dnew, *prow, *jrow, *red;
+    int *jpvt, *ipiv, *info;
+};
+
+__host__ __device__ inline size_t small_bytes(int N) {
+    // tau vn1 vn2 sv0-3 dnew prow jrow = 10 double vectors, red[64], jpvt ipiv int vectors, info
+    return (size_t)(10 * N + 64) * sizeof(double) + (size_t)(2 * N + 4) * sizeof(int);
+}
+
+__device__ inline void carve(Work& wk, const Params& p, int walker, int nmats_smem, unsigned char* smem) {
+    const int N = p.N;
+    double* s = reinterpret_cast<double*>(smem);
+    wk.tau = s;
+    wk.vn1 = s + N;
+    wk.vn2 = s + 2 * N;
+    for (int i = 0; i < 4; ++i) wk.sv[i] = s + (3 + i) * N;
+    wk.dnew = s + 7 * N;
+    wk.prow = s + 8 * N;
+    wk.jrow = s + 9 * N;
+    wk.red = s + 10 * N;
+    int* ip = reinterpret_cast<int*>(s + 10 * N + 64);
+    wk.jpvt = ip;
+    ip += N;
+    wk.ipiv = ip;
+    ip += N;
+    wk.info = ip;
+    double* tiles = reinterpret_cast<double*>(smem + ((small_bytes(N) + 15) & ~(size_t)15));
+    double* gws = p.ws + (size_t)walker * 3 * N * p.LD;
+    for (int i = 0; i < 3; ++i) {
+        if (i < nmats_smem) {
+            wk.b[i] = tiles + (size_t)i * N * p.LD;
+            wk.ld[i] = p.LD;
+        } else {
+            wk.b[i] = gws + (size_t)i * N * p.LD;
+            wk.ld[i] = p.LD;
+        }
+    }
+}
+
+__device__ inline double cta_reduce_sum(double v, double* red) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    v = warp_sum(v);
+    __syncthreads();
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    double t = 0.0;
+    for (int i = 0; i < nw; ++i) t += red[i];
+    return t;
+}
+__device__ inline double cta_reduce_max(double v, double* red) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    v = warp_max(v);
+    __syncthreads();
+    if (lane == 0) red[warp] = v;
+    __syncthreads();
+    double t = red[0];
+    for (int i = 1; i < nw; ++i) t = fmax(t, red[i]);
+    return t;
+}
+
+// --------------------------------------------------------------------------------------------------
+// stablelinalg::to_LDR (source/stablelinalg.cpp:35-55).  A is factorised in place (destroyed);
+// Q -> Qo, D^-1 R P^T -> Ro (both distinct from A), |diag R| -> dout (shared vector).
+// --------------------------------------------------------------------------------------------------
+__device__ void dev_to_ldr(Work& wk, int n, double* A, int lda, double* Qo, int ldq, double* Ro, int ldr, double* dout) {
+    __syncthreads();
+    cta_qrp(A, lda, n, wk.tau, wk.jpvt, wk.vn1, wk.vn2);
+    for (int j = threadIdx.x; j < n; j += blockDim.x) {
+        const double dj = fabs(A[j + (size_t)j * lda]);
+        dout[j] = dj;
+        wk.vn1[j] = 1.0 / dj;  // D_inv_vec (vn1 is free after the factorisation)
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
+        const int i = e % n, j = e / n;
+        const double v = (i <= j) ? wk.vn1[i] * A[i + (size_t)j * lda] : 0.0;
+        Ro[i + (size_t)wk.jpvt[j] * ldr] = v;  // R_final = R_normalized.cols(P_inv)
+    }
+    cta_form_q(Qo, ldq, A, lda, wk.tau, n);
+    __syncthreads();
+}
+
+// split d into D_large^-1 (or D_large) and D_small (source/stablelinalg.cpp:100-108)
+__device__ inline void split_d(const double* d, int n, double* dl_inv, double* ds) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const double v = d[i];
+        if (v >= 1.0) {
+            dl_inv[i] = 1.0 / v;
+            ds[i] = 1.0;
+        } else {
+            dl_inv[i] = 1.0;
+            ds[i] = v;
+        }
+    }
+}
+
+__device__ inline void set_diag(double* B, int ld, int n, const double* dvec) {
+    for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
+        const int r = e % n, c = e / n;
+        B[r + (size_t)c * ld] = (r == c) ? dvec[r] : 0.0;
+    }
+}
+
+__device__ inline void note_fail(const Params& p, const Work& wk, int code) {
+    if (threadIdx.x == 0 && *wk.info != 0) atomicCAS(p.fail, 0, code);
+}
+
+// --------------------------------------------------------------------------------------------------
+// stablelinalg::inv_I_plus_ldr (source/stablelinalg.cpp:94-126).  Result G in wk.b[1]; returns logdet.
+// --------------------------------------------------------------------------------------------------
+__device__ double dev_inv_I_plus_ldr(const Params& p, Work& wk, int n, const double* L, int ldl, const double* d, const double* R,
+                                     int ldr) {
+    double* b0 = wk.b[0];
+    double* b1 = wk.b[1];
+    double* b2 = wk.b[2];
+    const int l0 = wk.ld[0], l1 = wk.ld[1], l2 = wk.ld[2];
+    __syncthreads();
+    split_d(d, n, wk.sv[0], wk.sv[1]);
+    cta_copy(b0, l0, R, ldr, n);
+    __syncthreads();
+    double part = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) part += (d[i] >= 1.0) ? log(d[i]) : 0.0;  // sum log D_large
+    const double logdl = cta_reduce_sum(part, wk.red);
+    cta_lu(b0, l0, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    note_fail(p, wk, 10);
+    set_diag(b1, l1, n, wk.sv[0]);
+    __syncthreads();
+    cta_lu_solve(b0, l0, n, wk.ipiv, b1, 1, l1);  // X = R^-1 D_large^-1
+    __syncthreads();
+    for (int e = threadIdx.x; e < n * n; e += blockDim.x) {  // M = X + L D_small ; b0 <- M^T
+        const int r = e % n, c = e / n;
+        const double m = b1[r + (size_t)c * l1] + L[r + (size_t)c * ldl] * wk.sv[1][c];
+        b2[r + (size_t)c * l2] = m;
+        b0[c + (size_t)r * l0] = m;
+    }
+    __syncthreads();
+    cta_lu(b0, l0, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    note_fail(p, wk, 11);
+    part = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) part += log(fabs(b0[i + (size_t)i * l0]));
+    const double logm = cta_reduce_sum(part, wk.red);
+    // solve M^T Gt = X^T in place on X viewed transposed: the result is G column-major in b1
+    cta_lu_solve(b0, l0, n, wk.ipiv, b1, l1, 1);
+    __syncthreads();
+    return logdl + logm;
+}
+
+// --------------------------------------------------------------------------------------------------
+// stablelinalg::inv_I_plus_ldr_mul_ldr (source/stablelinalg.cpp:128-158).  Result G in wk.b[2].
+// --------------------------------------------------------------------------------------------------
+__device__ void dev_inv_I_plus_ldr_mul_ldr(const Params& p, Work& wk, int n, const double* L1, const double* d1, const double* R1,
+                                           const double* L2, const double* d2, const double* R2, int ldg) {
+    double* b0 = wk.b[0];
+    double* b1 = wk.b[1];
+    double* b2 = wk.b[2];
+    const int l0 = wk.ld[0], l1 = wk.ld[1], l2 = wk.ld[2];
+    __syncthreads();
+    split_d(d1, n, wk.sv[0], wk.sv[1]);
+    split_d(d2, n, wk.sv[2], wk.sv[3]);
+    cta_copy(b0, l0, R2, ldg, n);
+    __syncthreads();
+    cta_lu(b0, l0, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    note_fail(p, wk, 12);
+    set_diag(b1, l1, n, wk.sv[2]);
+    __syncthreads();
+    cta_lu_solve(b0, l0, n, wk.ipiv, b1, 1, l1);  // X = R2^-1 D2_large^-1
+    __syncthreads();
+    // TermA = D1l^-1 (L1^T X)
+    cta_gemm<false>(b2, l2, L1, ldg, 1, b1, 1, l1, n, wk.sv[0], nullptr);
+    // b0 = L2 D2s
+    cta_copy(b0, l0, L2, ldg, n, nullptr, wk.sv[3]);
+    __syncthreads();
+    // M = TermA + D1s (R1 (L2 D2s))
+    cta_gemm<true>(b2, l2, R1, 1, ldg, b0, 1, l0, n, wk.sv[1], nullptr);
+    __syncthreads();
+    // RHS = D1l^-1 L1^T  -> b0
+    for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
+        const int r = e % n, c = e / n;
+        b0[r + (size_t)c * l0] = wk.sv[0][r] * L1[c + (size_t)r * ldg];
+    }
+    __syncthreads();
+    cta_lu(b2, l2, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    note_fail(p, wk, 13);
+    cta_lu_solve(b2, l2, n, wk.ipiv, b0, 1, l0);  // Y = M^-1 RHS
+    __syncthreads();
+    cta_gemm<false>(b2, l2, b1, 1, l1, b0, 1, l0, n, nullptr, nullptr);  // G = X Y
+    __syncthreads();
+}
+
+// --------------------------------------------------------------------------------------------------
+// B-matrix helpers
+// --------------------------------------------------------------------------------------------------
+// DQMC::calculate_Bbar (source/dqmc.cpp:88-105): product of the block's B_l = diag(e^{V_l}) expK,
+// slices ascending, from the CURRENT fields.  Result in wk.b[0] (uses wk.b[1] as ping-pong).
+__device__ void dev_bbar(const Params& p, Work& wk, int walker, int i_stack) {
+    const int n = p.N;
+    const int l0 = i_stack * p.n_stab;
+    const int l1 = min(l0 + p.n_stab, p.nt);
+    const int8_t* f = p.fields + ((size_t)walker * p.nt) * n;
+    double* cur = ((l1 - l0) & 1) ? wk.b[0] : wk.b[1];  // so that the last product lands in b[0]
+    double* oth = ((l1 - l0) & 1) ? wk.b[1] : wk.b[0];
+    const int ldc = ((l1 - l0) & 1) ? wk.ld[0] : wk.ld[1];
+    const int ldo = ((l1 - l0) & 1) ? wk.ld[1] : wk.ld[0];
+    __syncthreads();
+    for (int i = threadIdx.x; i < n; i += blockDim.x) wk.sv[0][i] = p.lut_ev[f[(size_t)l0 * n + i]];
+    __syncthreads();
+    cta_copy(cur, ldc, p.expK, n, n, wk.sv[0], nullptr);  // B_{l0} (reference multiplies by the identity: exact)
+    __syncthreads();
+    int ldcur = ldc, ldoth = ldo;
+    for (int l = l0 + 1; l < l1; ++l) {
+        for (int i = threadIdx.x; i < n; i += blockDim.x) wk.sv[0][i] = p.lut_ev[f[(size_t)l * n + i]];
+        __syncthreads();
+        // B_l * Bbar = diag(ev) (expK * Bbar)
+        cta_gemm<false>(oth, ldoth, p.expK, 1, n, cur, 1, ldcur, n, wk.sv[0], nullptr);
+        __syncthreads();
+        double* t = cur;
+        cur = oth;
+        oth = t;
+        const int tl = ldcur;
+        ldcur = ldoth;
+        ldoth = tl;
+    }
+}
+
+// propagate_GF_forward: G <- B_l G B_l^-1 (source/dqmc.cpp:113-132).  G in g (ld ldg), scratch t.
+__device__ void dev_wrap_forward(const Params& p, int n, double* g, int ldg, double* t, int ldt, const double* ev, const double* iev) {
+    cta_gemm<false>(t, ldt, p.expK, 1, n, g, 1, ldg, n, nullptr, nullptr);
+    __syncthreads();
+    cta_gemm<false>(g, ldg, t, 1, ldt, p.invexpK, 1, n, n, ev, iev);
+    __syncthreads();
+}
+// propagate_GF_backward: G <- B_l^-1 G B_l (source/dqmc.cpp:169-187)
+__device__ void dev_wrap_backward(const Params& p, int n, double* g, int ldg, double* t, int ldt, const double* ev, const double* iev) {
+    // t = invexpK (diag(iev) G)   [reference: (invexpK diag(iev)) G — the same product up to rounding order]
+    for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
+        const int r = e % n, c = e / n;
+        g[r + (size_t)c * ldg] *= iev[r];
+    }
+    __syncthreads();
+    cta_gemm<false>(t, ldt, p.invexpK, 1, n, g, 1, ldg, n, nullptr, nullptr);
+    __syncthreads();
+    // g = (t diag(ev)) expK
+    for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
+        const int r = e % n, c = e / n;
+        t[r + (size_t)c * ldt] *= ev[c];
+    }
+    __syncthreads();
+    cta_gemm<false>(g, ldg, t, 1, ldt, p.expK, 1, n, n, nullptr, nullptr);
+    __syncthreads();
+}
+
+// --------------------------------------------------------------------------------------------------
+// RNG: Philox4x32-10 (throughput mode)
+// --------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c.x), lo0 = 0xD2511F53u * c.x;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c.z), lo1 = 0xCD9E8D57u * c.z;
+        c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+        k.x += 0x9E3779B9u;
+        k.y += 0xBB67AE85u;
+    }
+    return c;
+}
+
+// Fill the per-slice draw tables for one local_update call ("visit") of one walker.
+//   s_perm[N] visiting order, s_k[N] proposal index 0..2, s_u[N] uniform in [0,1)
+// skey: N uint32 scratch.
+__device__ void load_visit_draws(const Params& p, int walker, unsigned long long visit, int* s_perm, int* s_k, double* s_u,
+                                 uint32_t* skey) {
+    const int n = p.N;
+    if (p.rng_mode == DQMCB_RNG_PHILOX) {
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            const uint4 r = philox4x32_10(make_uint4((uint32_t)i, (uint32_t)visit, (uint32_t)(visit >> 32), (uint32_t)walker),
+                                          make_uint2((uint32_t)p.seed, (uint32_t)(p.seed >> 32)));
+            skey[i] = r.x;
+            s_k[i] = (int)__umulhi(r.y, 3u);
+            const unsigned long long bits = ((unsigned long long)r.w << 32) | r.z;
+            s_u[i] = (double)(bits >> 11) * (1.0 / 9007199254740992.0);
+        }
+        __syncthreads();
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {  // rank of key i = position in the random order
+            const uint32_t ki = skey[i];
+            int rank = 0;
+            for (int j = 0; j < n; ++j) {
+                const uint32_t kj = skey[j];
+                rank += (kj < ki) || (kj == ki && j < i);
+            }
+            s_perm[rank] = i;
+        }
+    } else {  // TAPE / MT19937: draws were staged in global memory in visiting order
+        const size_t off = ((size_t)walker * p.tape_visits + (size_t)(visit - p.visit_base)) * n;
+        for (int i = threadIdx.x; i < n; i += blockDim.x) {
+            s_perm[i] = p.tape_perm[off + i];
+            s_k[i] = p.tape_k[off + i];
+            s_u[i] = p.tape_u[off + i];
+        }
+    }
+    __syncthreads();
+}
+
+// --------------------------------------------------------------------------------------------------
+// update::local_update (source/update.cpp:5-32) with AttractiveHubbard::local_update_ratio /
+// update_greens_local (source/model.cpp:109-138): sequential Metropolis over the shuffled sites of
+// one slice, rank-1 Sherman-Morrison on accept.  Every thread evaluates the (identical) accept
+// decision, so no barrier is needed for rejected proposals.  The update uses separate multiply
+// and add (no FMA contraction), i.e. exactly the reference's `G += prefactor*U*V` rounding.
+// --------------------------------------------------------------------------------------------------
+__device__ int dev_local_update(const Params& p, int n, double* g, int ldg, int8_t* s_f, const int* s_perm, const int* s_k,
+                                const double* s_u, double* s_ucol, double* s_vrow) {
+    int accepted = 0;
+    for (int idx = 0; idx < n; ++idx) {
+        const int i = s_perm[idx];
+        const int oldf = s_f[i];
+        const int newf = s_k[idx] + (s_k[idx] >= oldf);  // k-th element of {0,1,2,3}\{old}, include/field.h:45-48
+        const double gii = g[i + (size_t)i * ldg];
+        const double delta = p.lut_delta[oldf * 4 + newf];
+        const double r = 1.0 + (1.0 - gii) * delta;
+        const double R = p.lut_gb[oldf * 4 + newf] * (r * r);
+        const double prob = fmin(1.0, fabs(R));
+        if (s_u[idx] < prob) {
+            ++accepted;
+            const double pref = delta / r;
+            for (int t = threadIdx.x; t < n; t += blockDim.x) {
+                s_ucol[t] = __dmul_rn(pref, g[t + (size_t)i * ldg]);
+                s_vrow[t] = g[i + (size_t)t * ldg] - ((t == i) ? 1.0 : 0.0);
+            }
+            __syncthreads();
+            for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
+                const int rr = e % n, cc = e / n;
+                double* ge = g + rr + (size_t)cc * ldg;
+                *ge = __dadd_rn(*ge, __dmul_rn(s_ucol[rr], s_vrow[cc]));
+            }
+            if (threadIdx.x == 0) s_f[i] = (int8_t)newf;
+            __syncthreads();
+        }
+    }
+    return accepted;
+}
+
+}  // namespace dq

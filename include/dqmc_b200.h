@@ -1,0 +1,157 @@
+/*
+ * dqmc_b200.h -- C ABI of the B200-native DQMC sweep hot path.
+ *
+ * This is the drop-in boundary for the reference's Armadillo/MKL path (kfkq/DQMC).  The
+ * reference has no FFI of its own; the boundary is its C++ surface, so each
+ * entry point below cites the reference function it replaces (paths relative to the reference
+ * root).  The C++ host mirror in include/dqmcb/ (same class / function names as the reference's
+ * headers) and the Python binding dqmc_b200/capi.py both sit on top of exactly these symbols.
+ *
+ * Conventions
+ *   - every call returns 0 on success, a DQMCB_E* code otherwise; dqmcb_last_error() gives text;
+ *   - all matrices are FP64, column-major, dense N x N (arma::mat layout);
+ *   - one context = W independent walkers (Markov chains) of one model on one GPU; all batched
+ *     calls act on every walker; host buffers are walker-major ([W][...]);
+ *   - work is enqueued on the context's CUDA stream (dqmcb_set_stream); only the get_* / host
+ *     buffer calls synchronise;
+ *   - there is NO CPU fallback: without a CUDA device every compute call fails with DQMCB_ECUDA.
+ */
+#ifndef DQMC_B200_H
+#define DQMC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DQMCB_OK 0
+#define DQMCB_EINVAL 1   /* bad argument (std::invalid_argument / std::out_of_range on the C++ side) */
+#define DQMCB_ECUDA 2    /* CUDA runtime failure or no device */
+#define DQMCB_ENUMERIC 3 /* factorisation failed (std::runtime_error, source/stablelinalg.cpp:43-45) */
+#define DQMCB_ESTATE 4   /* call order violated (e.g. sweep before init) */
+
+typedef struct dqmcb_ctx dqmcb_ctx;
+
+/* RNG modes for the Metropolis loop */
+#define DQMCB_RNG_TAPE 0   /* host-supplied tape (parity runs: replay of the reference's mt19937 stream) */
+#define DQMCB_RNG_PHILOX 1 /* Philox4x32-10 keyed on (seed, walker, visit counter, site) generated in-kernel */
+#define DQMCB_RNG_MT19937 2 /* device-resident std::mt19937 per walker reproducing libstdc++'s
+                               shuffle / uniform_int / bernoulli draws (source/update.cpp:10-25) */
+
+typedef struct {
+    int n_sites;   /* N = L1*L2 (model.ns(), include/model.h:49) */
+    int nt;        /* number of time slices */
+    int n_stab;    /* stabilisation interval (source/dqmc.cpp:9) */
+    int n_walkers; /* W independent chains batched on this GPU */
+    int device;    /* CUDA device ordinal */
+    int delay_k;   /* 0/1: rank-1 Sherman-Morrison per accepted flip (reference behaviour);
+                      k>1: delayed rank-k updates (algebraically identical) */
+    double g;      /* sqrt(|U| dtau / 2), source/model.cpp:27 */
+    double alpha;  /* -1 for the attractive model, source/model.cpp:28 */
+    double eta[4];   /* include/field.h:40-43 */
+    double gamma[4]; /* include/field.h:35-38 */
+} dqmcb_config;
+
+/* ---- lifetime ------------------------------------------------------------------------------- */
+/* AttractiveHubbard ctor + DQMC ctor (source/model.cpp:3-36, source/dqmc.cpp:5-36).  expK / invexpK
+ * are host N x N column-major exp(-/+ dtau K); K itself is built on the host (source/model.cpp:39-60). */
+int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* invexpK, dqmcb_ctx** out);
+void dqmcb_destroy(dqmcb_ctx* ctx);
+const char* dqmcb_last_error(const dqmcb_ctx* ctx); /* ctx may be NULL: last create() error */
+int dqmcb_set_stream(dqmcb_ctx* ctx, void* cuda_stream);
+int dqmcb_synchronize(dqmcb_ctx* ctx);
+int dqmcb_n_stack(const dqmcb_ctx* ctx); /* ceil(nt / n_stab), source/dqmc.cpp:10 */
+/* half-wrap matrices exp(-/+ dtau K / 2) for dqmcb_half_wrap (source/model.cpp:34-35) */
+int dqmcb_set_half_expK(dqmcb_ctx* ctx, const double* expK_half, const double* invexpK_half);
+
+/* ---- HS field (GHQField, include/field.h) ----------------------------------------------------- */
+/* Native device layout: int8 [W][nt][N].  The *_i64 forms take the reference's arma::imat layout
+ * (int64, nt x N column-major, include/field.h:52) for ONE walker. */
+int dqmcb_set_fields(dqmcb_ctx* ctx, const int8_t* fields);
+int dqmcb_get_fields(dqmcb_ctx* ctx, int8_t* fields);
+int dqmcb_set_fields_i64(dqmcb_ctx* ctx, int walker, const long long* fields);
+int dqmcb_get_fields_i64(dqmcb_ctx* ctx, int walker, long long* fields);
+
+/* ---- RNG ---------------------------------------------------------------------------------------- */
+int dqmcb_rng_mode(dqmcb_ctx* ctx, int mode, uint64_t seed);
+/* mode MT19937: one std::mt19937 seed per walker (utility::random ctor, include/utility.h:27) */
+int dqmcb_rng_seed_mt19937(dqmcb_ctx* ctx, const uint32_t* seeds);
+/* mode TAPE: draws for the next `n_visits` local_update calls of every walker, in visiting order:
+ * perm[W][n_visits][N] site order, knew[W][n_visits][N] proposal index 0..2, u[W][n_visits][N]. */
+int dqmcb_set_tape(dqmcb_ctx* ctx, int n_visits, const uint8_t* perm, const uint8_t* knew, const double* u);
+
+/* ---- stacks and Green's functions (source/dqmc.cpp:43-72) -------------------------------------- */
+int dqmcb_init_stacks(dqmcb_ctx* ctx);         /* DQMC::init_stacks            */
+int dqmcb_init_greenfunctions(dqmcb_ctx* ctx); /* DQMC::init_greenfunctions -> G(0), log_det_M */
+
+/* ---- single steps of the sweep (teacher-forced parity; DQMC's private helpers) ----------------- */
+int dqmcb_wrap_forward(dqmcb_ctx* ctx, int l);  /* propagate_GF_forward,  source/dqmc.cpp:113-132 */
+int dqmcb_wrap_backward(dqmcb_ctx* ctx, int l); /* propagate_GF_backward, source/dqmc.cpp:169-187 */
+int dqmcb_local_update(dqmcb_ctx* ctx, int l);  /* update::local_update,  source/update.cpp:5-32  */
+int dqmcb_block_product(dqmcb_ctx* ctx, int i_stack); /* calculate_Bbar, source/dqmc.cpp:88-105 (into ctx Bbar) */
+int dqmcb_get_block_product(dqmcb_ctx* ctx, double* Bbar /* [W][N*N] */);
+/* update_stack_* + stabilize_GF_* + check_error at the end of block i_stack (source/dqmc.cpp:369-394,
+ * 429-454), using the Bbar computed from the current fields. */
+int dqmcb_stabilize_forward(dqmcb_ctx* ctx, int l);
+int dqmcb_stabilize_backward(dqmcb_ctx* ctx, int l);
+
+/* ---- whole sweeps (source/dqmc.cpp:337-396, 398-456) -------------------------------------------- */
+int dqmcb_sweep_0_to_beta(dqmcb_ctx* ctx);
+int dqmcb_sweep_beta_to_0(dqmcb_ctx* ctx);
+
+/* ---- state access -------------------------------------------------------------------------------- */
+int dqmcb_get_G(dqmcb_ctx* ctx, double* G /* [W][N*N] */); /* current equal-time G of every walker */
+int dqmcb_set_G(dqmcb_ctx* ctx, const double* G);
+int dqmcb_get_ldr(dqmcb_ctx* ctx, int i_stack, double* L, double* d, double* R); /* [W][N*N],[W][N],[W][N*N] */
+int dqmcb_set_ldr(dqmcb_ctx* ctx, int i_stack, const double* L, const double* d, const double* R);
+int dqmcb_get_logdet(dqmcb_ctx* ctx, double* logdet /* [W] */); /* GF::log_det_M */
+/* acc_rate(), max_err(), mean_err() of include/dqmc.h:80-82, per walker ([W] each, any may be NULL) */
+int dqmcb_get_stats(dqmcb_ctx* ctx, double* acc_rate, double* max_err, double* mean_err);
+int dqmcb_reset_stats(dqmcb_ctx* ctx);
+/* raw device pointers for zero-copy interop (NCCL field swaps, torch views) */
+#define DQMCB_PTR_FIELDS 0
+#define DQMCB_PTR_G 1
+#define DQMCB_PTR_LOGDET 2
+#define DQMCB_PTR_OBS 3
+void* dqmcb_device_ptr(dqmcb_ctx* ctx, int which);
+
+/* ---- measurements / action ------------------------------------------------------------------------ */
+/* Observables::calculate_{density,doubleOccupancy,swavePairing,densityCorr} (source/model.cpp:167-288)
+ * from the current G: scalars[W][3], corr[W][N*N] (may be NULL). */
+int dqmcb_measure_equal_time(dqmcb_ctx* ctx, double* scalars, double* corr);
+/* AttractiveHubbard::global_action, source/model.cpp:140-159: S[W] */
+int dqmcb_global_action(dqmcb_ctx* ctx, double* S);
+/* DQMC::half_warp, equal-time entry (source/dqmc.cpp:288-315): Gsym[W][N*N] = invexpKhalf G expKhalf */
+int dqmcb_half_wrap(dqmcb_ctx* ctx, double* Gsym);
+
+/* ---- end-to-end convenience: host fields in, one full sweep, host results out ------------------------ */
+/* set_fields + init_stacks + init_greenfunctions happen only if `reinit` != 0; then n_sweeps x
+ * (sweep_0_to_beta; sweep_beta_to_0); then fields, scalars (and G if non-NULL) are copied back. */
+int dqmcb_run_sweeps_host(dqmcb_ctx* ctx, int reinit, const int8_t* fields_in, int n_sweeps, int8_t* fields_out,
+                          double* scalars_out, double* G_out);
+
+/* ---- stand-alone batched stablelinalg (source/stablelinalg.cpp), host buffers, `batch` problems ---- */
+int dqmcb_to_LDR(int device, int n, int batch, const double* M, double* L, double* d, double* R);
+int dqmcb_mat_mul_ldr(int device, int n, int batch, const double* M, const double* L, const double* d, const double* R,
+                      double* Lo, double* dO, double* Ro);
+int dqmcb_ldr_mul_mat(int device, int n, int batch, const double* L, const double* d, const double* R, const double* M,
+                      double* Lo, double* dO, double* Ro);
+int dqmcb_ldr_mul_ldr(int device, int n, int batch, const double* L1, const double* d1, const double* R1, const double* L2,
+                      const double* d2, const double* R2, double* Lo, double* dO, double* Ro);
+int dqmcb_inv_I_plus_ldr(int device, int n, int batch, const double* L, const double* d, const double* R, double* G,
+                         double* logdet);
+int dqmcb_inv_I_plus_ldr_mul_ldr(int device, int n, int batch, const double* L1, const double* d1, const double* R1,
+                                 const double* L2, const double* d2, const double* R2, double* G);
+
+/* update::partner_rank, source/update.cpp:34-45 (pure host arithmetic) */
+int dqmcb_partner_rank(int rank, int world_size, int exchange_attempt);
+
+/* library build info, e.g. "dqmc_b200 sm_100a" */
+const char* dqmcb_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DQMC_B200_H */

@@ -1,0 +1,191 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle on identical inputs.
+
+Tolerance: 1e-10 relative (max-norm), the bar BASELINE.json's north_star states; accept/reject
+decisions and fields must be identical.  Chaotic wrap drift is handled as the survey
+prescribes: per-step checks are teacher-forced, trajectories compare decisions/fields exactly and
+G at stabilisation points.
+"""
+import numpy as np
+import pytest
+
+from oracle import dqmc_oracle as O
+from tests.common import CONFIGS, make_ctx, make_oracle, rel_err
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-10
+
+
+def _setup(name, seeds):
+    cfg = CONFIGS[name]
+    pairs = [make_oracle(cfg, s) for s in seeds]
+    m0 = pairs[0][0]
+    ctx = make_ctx(cfg, len(seeds), m0.expK, m0.invexpK)
+    for m, _ in pairs:  # all walkers share the model matrices bit-for-bit
+        m.expK, m.invexpK = m0.expK, m0.invexpK
+    ctx.set_fields(np.stack([m.fields for m, _ in pairs]).astype(np.int8))
+    return cfg, pairs, ctx
+
+
+@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "C2s"])
+def test_init_stacks_and_green(name):
+    cfg, pairs, ctx = _setup(name, [11, 12, 13])
+    ctx.init_stacks()
+    ctx.init_greenfunctions()
+    G = ctx.get_G()
+    logdet = ctx.get_logdet()
+    for w, (m, d) in enumerate(pairs):
+        d.init_stacks()
+        d.init_greenfunctions()
+        assert rel_err(G[w], d.G) < TOL
+        assert abs(logdet[w] - d.log_det_M) < TOL * max(1.0, abs(d.log_det_M))
+    for i in range(ctx.n_stack):
+        Lm, dd, Rm = ctx.get_ldr(i)
+        for w, (m, d) in enumerate(pairs):
+            F = d.stack[i]
+            prod = (Lm[w] * dd[w]) @ Rm[w]
+            assert rel_err(prod, F.to_matrix()) < 1e-9
+            assert np.allclose(np.sort(dd[w]), np.sort(F.d), rtol=1e-9)
+            assert np.allclose(Lm[w].T @ Lm[w], np.eye(m.ns), atol=1e-12)
+
+
+@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "C2s"])
+def test_wrap_steps_teacher_forced(name):
+    cfg, pairs, ctx = _setup(name, [21, 22])
+    rng = np.random.default_rng(5)
+    n = pairs[0][0].ns
+    G0 = np.stack([np.eye(n) * 0.5 + 0.1 * rng.standard_normal((n, n)) for _ in pairs])
+    for l in (0, 3, cfg[6] - 1):
+        ctx.set_G(G0)
+        ctx.wrap_forward(l)
+        Gf = ctx.get_G()
+        ctx.set_G(G0)
+        ctx.wrap_backward(l)
+        Gb = ctx.get_G()
+        for w, (m, d) in enumerate(pairs):
+            assert rel_err(Gf[w], d.wrap_forward(G0[w], l)) < TOL
+            assert rel_err(Gb[w], d.wrap_backward(G0[w], l)) < TOL
+
+
+@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "C2s"])
+def test_block_product(name):
+    cfg, pairs, ctx = _setup(name, [31, 32])
+    for i in range(ctx.n_stack):
+        B = ctx.block_product(i)
+        for w, (m, d) in enumerate(pairs):
+            assert rel_err(B[w], d.calculate_Bbar(i)) < TOL
+
+
+@pytest.mark.parametrize("name", ["C0", "C1s", "R7"])
+def test_local_update_teacher_forced(name):
+    """One slice of Metropolis from the oracle's G: identical decisions and fields, G to 1e-10."""
+    cfg, pairs, ctx = _setup(name, [41, 42, 43])
+    n, nt = pairs[0][0].ns, cfg[6]
+    gens = [O.MT19937(100 + w) for w in range(len(pairs))]
+    tapes = [O.rng_tape(g, n, 2) for g in gens]
+    ctx.set_tape(np.stack([t[0] for t in tapes]), np.stack([t[1] for t in tapes]), np.stack([t[2] for t in tapes]))
+    Gin = []
+    for m, d in pairs:
+        d.init_stacks()
+        d.init_greenfunctions()
+        Gin.append(d.wrap_forward(d.G, 0))
+    ctx.set_G(np.stack(Gin))
+    for visit, l in enumerate((0, nt - 1)):
+        ctx.local_update(l)
+        G = ctx.get_G()
+        f = ctx.get_fields()
+        for w, (m, d) in enumerate(pairs):
+            Gw = Gin[w] if visit == 0 else G_prev[w]
+            Gw = Gw.copy()
+            d.local_update(Gw, l, tapes[w][0][visit], tapes[w][1][visit], tapes[w][2][visit])
+            assert np.array_equal(f[w], m.fields)
+            assert rel_err(G[w], Gw) < TOL
+        G_prev = G
+
+
+@pytest.mark.parametrize("name,n_sweeps", [("C0", 3), ("C1s", 3), ("R7", 3), ("C2s", 1)])
+def test_trajectory(name, n_sweeps):
+    """Free-running sweeps on the same RNG tape: identical accept decisions / fields; G compared at
+    the end of each half sweep (a stabilisation point, where G is a function of the fields only)."""
+    cfg, pairs, ctx = _setup(name, [51, 52])
+    n, nt = pairs[0][0].ns, cfg[6]
+    gens = [O.MT19937(200 + w) for w in range(len(pairs))]
+    ctx.init_stacks()
+    ctx.init_greenfunctions()
+    for m, d in pairs:
+        d.init_stacks()
+        d.init_greenfunctions()
+    for s in range(n_sweeps):
+        tapes = [O.rng_tape(g, n, 2 * nt) for g in gens]
+        ctx.set_tape(np.stack([t[0] for t in tapes]), np.stack([t[1] for t in tapes]), np.stack([t[2] for t in tapes]))
+        ctx.sweep_0_to_beta()
+        Gf = ctx.get_G()
+        ff = ctx.get_fields()
+        ctx.sweep_beta_to_0()
+        Gb = ctx.get_G()
+        fb = ctx.get_fields()
+        for w, (m, d) in enumerate(pairs):
+            t = tapes[w]
+            d.sweep_0_to_beta((t[0][:nt], t[1][:nt], t[2][:nt]))
+            assert np.array_equal(ff[w], m.fields), f"fields diverged in forward sweep {s}"
+            assert rel_err(Gf[w], d.G) < 1e-9
+            d.sweep_beta_to_0((t[0][nt:], t[1][nt:], t[2][nt:]))
+            assert np.array_equal(fb[w], m.fields), f"fields diverged in backward sweep {s}"
+            assert rel_err(Gb[w], d.G) < 1e-9
+    acc, emax, emean = ctx.get_stats()
+    for w, (m, d) in enumerate(pairs):
+        assert abs(acc[w] - d.acc_rate) < 1e-12
+        assert emax[w] < 1e-4
+    logdet = ctx.get_logdet()
+    S = ctx.global_action()
+    sc, corr = ctx.measure_equal_time()
+    for w, (m, d) in enumerate(pairs):
+        assert abs(logdet[w] - d.log_det_M) < 1e-9 * abs(d.log_det_M)
+        assert abs(S[w] - m.global_action(d.log_det_M)) < 1e-9 * abs(S[w])
+        den, docc, sw, cc = O.observables(d.G)
+        assert abs(sc[w, 0] - den) < 1e-9 and abs(sc[w, 1] - docc) < 1e-9 and abs(sc[w, 2] - sw) < 1e-9
+        assert rel_err(corr[w], cc) < 1e-9
+
+
+@pytest.mark.parametrize("n", [36, 64, 35])
+def test_stablelinalg_batched(n):
+    """source/stablelinalg.cpp functions one by one on graded random matrices."""
+    from dqmc_b200 import capi
+
+    rng = np.random.default_rng(n)
+    b = 3
+
+    def graded():
+        Q1, _ = np.linalg.qr(rng.standard_normal((n, n)))
+        Q2, _ = np.linalg.qr(rng.standard_normal((n, n)))
+        s = np.exp(np.linspace(6, -6, n))
+        return (Q1 * s) @ Q2
+
+    Ms = np.stack([graded() for _ in range(b)])
+    Lg, dg, Rg = capi.to_LDR(Ms)
+    F = []
+    for i in range(b):
+        Fo = O.to_LDR(Ms[i])
+        F.append(Fo)
+        assert rel_err((Lg[i] * dg[i]) @ Rg[i], Ms[i]) < 1e-12
+        assert np.allclose(dg[i], Fo.d, rtol=1e-10)
+        assert rel_err(np.abs(Lg[i]), np.abs(Fo.L)) < 1e-8
+    M2 = np.stack([graded() for _ in range(b)])
+    F2 = [O.to_LDR(M2[i]) for i in range(b)]
+    pack = lambda Fs: (np.stack([f.L for f in Fs]), np.stack([f.d for f in Fs]), np.stack([f.R for f in Fs]))
+    out = capi.mat_mul_ldr(M2, pack(F))
+    for i in range(b):
+        assert rel_err((out[0][i] * out[1][i]) @ out[2][i], O.mat_mul_ldr(M2[i], F[i]).to_matrix()) < 1e-10
+    out = capi.ldr_mul_mat(pack(F), M2)
+    for i in range(b):
+        assert rel_err((out[0][i] * out[1][i]) @ out[2][i], O.ldr_mul_mat(F[i], M2[i]).to_matrix()) < 1e-10
+    out = capi.ldr_mul_ldr(pack(F), pack(F2))
+    for i in range(b):
+        assert rel_err((out[0][i] * out[1][i]) @ out[2][i], O.ldr_mul_ldr(F[i], F2[i]).to_matrix()) < 1e-10
+    G, ld = capi.inv_I_plus_ldr(pack(F))
+    for i in range(b):
+        Go, ldo = O.inv_I_plus_ldr(F[i])
+        assert rel_err(G[i], Go) < TOL
+        assert abs(ld[i] - ldo) < 1e-10 * max(1.0, abs(ldo))
+    G = capi.inv_I_plus_ldr_mul_ldr(pack(F), pack(F2))
+    for i in range(b):
+        assert rel_err(G[i], O.inv_I_plus_ldr_mul_ldr(F[i], F2[i])) < TOL

@@ -1,0 +1,356 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the DQMC sweep hot path (BASELINE.json metric:
+site-flips/sec and sweeps/sec per box).
+
+A "step" is one full sweep (sweep_0_to_beta + sweep_beta_to_0, source/main.cpp:156-157) of every
+walker on every GPU.  Workload at N=1 GPU: config C1 of BASELINE.json ("Hubbard 8x8 U=4 beta=8
+half-filling, 1024 batched walkers per GPU"), nt = 80 (dtau = 0.1), n_stab = 10.  Walkers shard
+across ranks with no data-path collective (weak scaling: 1024 walkers per GPU).
+
+    python bench.py --gpus N --steps K --warmup W            # our arm (CUDA, through the C ABI)
+    python bench.py --impl reference --gpus N ...            # reference CPU arm (oracle/_ref)
+
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (L1, L2, U, t, mu, beta, nt, n_stab, walkers_per_gpu)
+    "C1": (8, 8, 4.0, 1.0, 0.0, 8.0, 80, 10, 1024),
+    "C0": (6, 6, 4.0, 1.0, -0.1, 4.0, 40, 10, 1024),
+    "C2": (12, 12, 4.0, 1.0, 0.0, 10.0, 100, 10, 296),
+    "C3": (16, 16, 6.0, 1.0, 0.0, 16.0, 160, 10, 148),
+}
+METRIC = "site_flips_per_sec"
+UNIT = "site-flips/s"
+
+
+def workload_desc(name, wl, n_gpus):
+    L1, L2, U, t, mu, beta, nt, n_stab, W = wl
+    return {
+        "workload": f"{name}: attractive Hubbard {L1}x{L2} U={U:g} mu={mu:g} beta={beta:g} nt={nt} n_stab={n_stab}, "
+                    f"{W} walkers/GPU, 1 step = 1 full sweep (fwd+bwd) of every walker",
+        "lattice": f"{L1}x{L2}", "U": U, "beta": beta, "nt": nt, "n_stab": n_stab,
+        "walkers_per_gpu": W, "walkers_total": W * n_gpus,
+        "proposals_per_step": 2 * nt * L1 * L2 * W * n_gpus,
+        "l2_policy": "working set (LDR stacks %.0f MB/GPU) larger than the 126 MB L2" % (W * ((nt + n_stab - 1) // n_stab) * (2 * (L1 * L2) ** 2 + L1 * L2) * 8 / 1e6),
+        "parallelism": f"walkers sharded over {n_gpus} GPU(s), no data-path collective",
+    }
+
+
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    """Samples SM clock / throttle reasons with nvidia-smi while the timed region runs."""
+
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index: int):
+        self.index = index
+        self.samples = []
+        self._stop = threading.Event()
+        self._t = None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
+                                     capture_output=True, text=True, timeout=5).stdout.strip()
+                if out:
+                    self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def __enter__(self):
+        self._t = threading.Thread(target=self._run, daemon=True)
+        self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._t.join(timeout=6)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        sm = sorted(float(s[0]) for s in self.samples if s[0].replace(".", "").isdigit())
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(s) > 3 + i and s[3 + i].lower().startswith("active") for s in self.samples)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": float(self.samples[0][1]),
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def measured_peaks():
+    p = {}
+    for fn in ("MEASURED_PEAKS.json", os.path.join("profiles", "fp64_smem_peaks.json")):
+        try:
+            with open(os.path.join(ROOT, fn)) as f:
+                p.update(json.load(f))
+        except Exception:
+            pass
+    return p
+
+
+# ------------------------------------------------------------------------------------------------
+def cpu_reference_run(wl, n_chains, n_sweeps, warm_sweeps, seed0=1000):
+    """Times the reference's own CPU sweep loop (oracle/_ref = its unmodified sources) on
+    n_chains host threads, one independent chain each.  Returns (flips/s, sweeps/s, seconds)."""
+    from oracle import ref
+
+    if not ref.available():
+        raise RuntimeError("oracle/_ref/libdqmc_ref.so missing")
+    L1, L2, U, t, mu, beta, nt, n_stab, _ = wl
+    import io
+    import contextlib
+
+    sims = [ref.RefSim(L1, L2, U, t, mu, beta, nt, n_stab, seed0 + i) for i in range(n_chains)]
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    saved = os.dup(2)
+    os.dup2(devnull, 2)  # the reference prints a precision warning per stabilisation from random starts
+    try:
+        if warm_sweeps:
+            ref.run_sweeps(sims, warm_sweeps)
+        secs = ref.run_sweeps(sims, n_sweeps)
+    finally:
+        os.dup2(saved, 2)
+        os.close(devnull)
+        os.close(saved)
+    sweeps = n_chains * n_sweeps
+    return sweeps * 2 * nt * L1 * L2 / secs, sweeps / secs, secs
+
+
+def run_reference_arm(args, wl, name):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    chains = cores
+    per_step = 1 if wl[0] * wl[1] >= 64 else 4
+    L1, L2, U, t, mu, beta, nt, n_stab, W = wl
+    from oracle import ref
+
+    if not ref.available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libdqmc_ref.so was not built (needs /root/reference at build time)"}))
+        return
+    sims = [ref.RefSim(L1, L2, U, t, mu, beta, nt, n_stab, 1000 + i) for i in range(chains)]
+    devnull = os.open(os.devnull, os.O_WRONLY)
+    saved = os.dup(2)
+    os.dup2(devnull, 2)
+    try:
+        for _ in range(args.warmup):
+            ref.run_sweeps(sims, per_step)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            ref.run_sweeps(sims, per_step)
+        secs = time.perf_counter() - t0
+    finally:
+        os.dup2(saved, 2)
+        os.close(devnull)
+        os.close(saved)
+    sweeps = chains * per_step * args.steps
+    flips = sweeps * 2 * nt * L1 * L2
+    value = flips / secs
+    sample = f"{chains} independent chains (one per host thread) x {per_step} full sweep(s) per step, OpenBLAS pinned to 1 thread per chain"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_desc(name, wl, args.gpus),
+        "sweeps_per_sec": sweeps / secs,
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": chains, "kind": "reference", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+
+
+# ------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="C1", choices=list(WORKLOADS))
+    ap.add_argument("--walkers", type=int, default=0, help="override walkers per GPU")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    wl = list(WORKLOADS[args.workload])
+    if args.walkers:
+        wl[8] = args.walkers
+    wl = tuple(wl)
+    if args.impl == "reference":
+        run_reference_arm(args, wl, args.workload)
+        return
+
+    import torch
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the dqmc_b200 product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    from dqmc_b200 import capi, host
+
+    L1, L2, U, t, mu, beta, nt, n_stab, W = wl
+    N = L1 * L2
+    model = host.AttractiveHubbard(L1, L2, U, t, mu, beta, nt, n_stab, W, device=local_rank)
+    ctx = model.ctx
+    stream = torch.cuda.Stream(device=local_rank)
+    ctx.set_stream(stream.cuda_stream)
+    model.random_fields(1234 + rank)
+    ctx.rng_mode(capi.RNG_PHILOX, 99 + rank)
+    ctx.init_stacks()
+    ctx.init_greenfunctions()
+    ctx.synchronize()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step():
+        ctx.sweep_0_to_beta()
+        ctx.sweep_beta_to_0()
+
+    # ---- kernel-resident throughput (`value`) ----
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    ctx.timing_enable(True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local_rank) as clocks:
+        barrier()
+        with torch.cuda.stream(stream):
+            e0.record(stream)
+            for _ in range(args.steps):
+                step()
+            e1.record(stream)
+        barrier()
+    ms = e0.elapsed_time(e1)
+    kms, kn = ctx.timing_get()
+    ctx.timing_enable(False)
+    tms = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    ms_max = float(tms.item())
+    total_walkers = W * world
+    flips_per_step = 2 * nt * N * total_walkers
+    value = flips_per_step * args.steps / (ms_max * 1e-3)
+    sweeps_per_sec = total_walkers * args.steps / (ms_max * 1e-3)
+    acc, emax, emean = ctx.get_stats()
+
+    # ---- end to end through the C ABI with HOST buffers (`e2e`) ----
+    # per step: pinned host RNG tape for the sweep (the reference's rng argument of local_update)
+    # H2D, fwd+bwd sweep, measurement, then fields + observables D2H.
+    gen = np.random.default_rng(7 + rank)
+    visits = 2 * nt
+    pin = lambda shape, dt: torch.empty(shape, dtype=dt, pin_memory=True)
+    t_perm, t_k, t_u = pin((W, visits, N), torch.uint8), pin((W, visits, N), torch.uint8), pin((W, visits, N), torch.float64)
+    base = np.tile(np.arange(N, dtype=np.uint8), (W, visits, 1))
+    t_perm.numpy()[:] = gen.permuted(base, axis=-1)
+    t_k.numpy()[:] = gen.integers(0, 3, size=(W, visits, N), dtype=np.uint8)
+    t_u.numpy()[:] = gen.random((W, visits, N))
+    h2d = t_perm.numel() + t_k.numel() + t_u.numel() * 8
+    d2h = W * nt * N + W * 3 * 8
+
+    def e2e_step():
+        ctx.set_tape(t_perm.numpy(), t_k.numpy(), t_u.numpy())
+        return ctx.run_sweeps_host(None, 1)
+
+    for _ in range(max(1, min(args.warmup, 2))):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
+    if dist is not None:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = flips_per_step * args.steps / float(te.item())
+    ctx.rng_mode(capi.RNG_PHILOX, 99 + rank)
+
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel class ----
+    peaks = measured_peaks()
+    dom = int(np.argmax(kms[:2]))
+    dom_name = ["propagate (wrap + Metropolis)", "stabilize (Bbar + LDR stack + G)"][dom]
+    acc_rate = float(acc.mean()) / (2.0 * (args.steps + args.warmup)) if acc.size else 0.5
+    a = min(max(acc_rate, 0.0), 1.0)
+    n3 = float(N) ** 3
+    # algorithmic FP64 flops per launch: propagate launch = n_stab slices x
+    # (wrap 4N^3 + accepted flips a*N*2N^2) per walker; stabilize launch = Bbar 2N^3(n_stab-1) +
+    # ~18N^3 (2 GEMM + QRP + Q + 2 LU solves + 3 GEMM) per walker
+    flops_prop = W * n_stab * (4.0 * n3 + a * 2.0 * n3)
+    flops_stab = W * (2.0 * n3 * (n_stab - 1) + 18.0 * n3)
+    fl = [flops_prop, flops_stab][dom]
+    avg_ms = kms[dom] / max(int(kn[dom]), 1)
+    achieved = fl / (avg_ms * 1e-3) / 1e12
+    peak = peaks.get("fp64_dmma_m8n8k4_tflops")
+    roofline = {
+        "bound": "tensor", "kernel": dom_name, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
+        "frac": (achieved / peak) if peak else None, "traffic": None,
+        "peak_source": "FP64 DMMA m8n8k4 peak measured on this pool's B200 by benchmarks/peaks.cu (profiles/fp64_smem_peaks.json); "
+                       "MEASURED_PEAKS.json carries no FP64 figure",
+        "avg_launch_ms": avg_ms, "share_of_step": float(kms[dom] / max(kms.sum(), 1e-9)),
+        "class_ms": {"propagate": float(kms[0]), "stabilize": float(kms[1])},
+    }
+
+    cpu_baseline = None
+    if not args.no_cpu_baseline:
+        try:
+            cores = os.cpu_count() or 1
+            ns = 2 if N >= 64 else 8
+            v, sps, secs = cpu_reference_run(wl, cores, ns, 1)
+            cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sweeps_per_sec": sps,
+                            "sample": f"{cores} independent chains (one per host thread) x {ns} full sweeps of the same model, "
+                                      f"reference sources compiled unmodified (oracle/_ref), OpenBLAS 1 thread/chain, {secs:.1f} s wall"}
+        except Exception as ex:  # the oracle always exists in-tree; report loudly if the binary is missing
+            cpu_baseline = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {ex}"}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic", "config": workload_desc(args.workload, wl, world),
+        "sweeps_per_sec": sweeps_per_sec, "acceptance": a, "max_wrap_err": float(emax.max()),
+        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d) * world, "d2h_bytes_per_step": int(d2h) * world,
+                "path": "dqmcb_set_tape (pinned host RNG tape) + dqmcb_run_sweeps_host (fwd+bwd sweep, measure, fields+observables D2H)"},
+        "gpu_launches": int(kn.sum()),
+        "clocks": clocks.summary(),
+        "roofline": roofline,
+        "cpu_baseline": cpu_baseline,
+    }
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

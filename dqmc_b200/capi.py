@@ -49,6 +49,7 @@ SYMBOLS = [
     "dqmcb_reset_stats", "dqmcb_device_ptr", "dqmcb_measure_equal_time", "dqmcb_global_action", "dqmcb_half_wrap",
     "dqmcb_run_sweeps_host", "dqmcb_to_LDR", "dqmcb_mat_mul_ldr", "dqmcb_ldr_mul_mat", "dqmcb_ldr_mul_ldr",
     "dqmcb_inv_I_plus_ldr", "dqmcb_inv_I_plus_ldr_mul_ldr", "dqmcb_partner_rank", "dqmcb_version",
+    "dqmcb_timing_enable", "dqmcb_timing_get",
 ]
 
 
@@ -238,6 +239,18 @@ class Context:
 
     def reset_stats(self):
         self._ck(self.L.dqmcb_reset_stats(self.h))
+
+    def timing_enable(self, on=True):
+        self._ck(self.L.dqmcb_timing_enable(self.h, int(on)))
+
+    def timing_get(self):
+        ms = np.zeros(4)
+        n = np.zeros(4, dtype=np.int64)
+        self._ck(self.L.dqmcb_timing_get(self.h, _d(ms), n.ctypes.data_as(C.POINTER(C.c_longlong))))
+        return ms, n
+
+    def set_stream(self, cuda_stream_handle: int):
+        self._ck(self.L.dqmcb_set_stream(self.h, C.c_void_p(cuda_stream_handle)))
 
     def device_ptr(self, which: int) -> int:
         return self.L.dqmcb_device_ptr(self.h, which)

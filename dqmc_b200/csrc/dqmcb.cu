@@ -391,7 +391,61 @@ static void fill_luts(const dqmcb_config& c, Params& p) {
     }
 }
 
+struct TimeScope {
+    dqmcb_ctx* c;
+    dqmcb_ctx::Span sp;
+    bool on;
+    TimeScope(dqmcb_ctx* ctx, int cls) : c(ctx), on(ctx->timing) {
+        if (!on) return;
+        sp.cls = cls;
+        cudaEventCreate(&sp.a);
+        cudaEventCreate(&sp.b);
+        cudaEventRecord(sp.a, c->stream);
+    }
+    ~TimeScope() {
+        if (!on) return;
+        cudaEventRecord(sp.b, c->stream);
+        c->spans.push_back(sp);
+    }
+};
+
+static void drain_spans(dqmcb_ctx* ctx) {
+    for (auto& sp : ctx->spans) {
+        cudaEventSynchronize(sp.b);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, sp.a, sp.b);
+        ctx->t_ms[sp.cls] += ms;
+        ctx->t_n[sp.cls] += 1;
+        cudaEventDestroy(sp.a);
+        cudaEventDestroy(sp.b);
+    }
+    ctx->spans.clear();
+}
+
 extern "C" {
+
+int dqmcb_timing_enable(dqmcb_ctx* ctx, int on) {
+    if (!ctx) return DQMCB_EINVAL;
+    cudaSetDevice(ctx->cfg.device);
+    drain_spans(ctx);
+    ctx->timing = on != 0;
+    if (on)
+        for (int i = 0; i < DQMCB_K_CLASSES; ++i) {
+            ctx->t_ms[i] = 0.0;
+            ctx->t_n[i] = 0;
+        }
+    return DQMCB_OK;
+}
+int dqmcb_timing_get(dqmcb_ctx* ctx, double* ms, long long* launches) {
+    if (!ctx) return DQMCB_EINVAL;
+    cudaSetDevice(ctx->cfg.device);
+    drain_spans(ctx);
+    for (int i = 0; i < DQMCB_K_CLASSES; ++i) {
+        if (ms) ms[i] = ctx->t_ms[i];
+        if (launches) launches[i] = ctx->t_n[i];
+    }
+    return DQMCB_OK;
+}
 
 const char* dqmcb_version(void) { return "dqmc_b200 0.1 (sm_100a)"; }
 
@@ -530,6 +584,7 @@ void dqmcb_destroy(dqmcb_ctx* ctx) {
     cudaFree(ctx->d_tape_k);
     cudaFree(ctx->d_tape_u);
     cudaFree(ctx->d_mt);
+    drain_spans(ctx);
     delete ctx;
 }
 
@@ -687,6 +742,7 @@ static int launch_propagate(dqmcb_ctx* ctx, int l_first, int n_slices, int dir, 
     }
     Params p = ctx->p;
     if (p.rng_mode != DQMCB_RNG_TAPE) p.visit_base = 0;
+    TimeScope ts(ctx, DQMCB_K_PROPAGATE);
     if (fast64_available(ctx)) return fast64_propagate(ctx, p, l_first, n_slices, dir, v0, flags);
     k_propagate<<<p.W, kThreads, ctx->smem_prop, ctx->stream>>>(p, l_first, n_slices, dir, v0, flags);
     CK(cudaGetLastError());
@@ -695,6 +751,7 @@ static int launch_propagate(dqmcb_ctx* ctx, int l_first, int n_slices, int dir, 
 
 int dqmcb_init_stacks(dqmcb_ctx* ctx) {
     NEED(ctx);
+    TimeScope ts(ctx, DQMCB_K_INIT);
     k_init_stacks<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p);
     CK(cudaGetLastError());
     ctx->stacks_ready = true;
@@ -706,6 +763,7 @@ int dqmcb_init_greenfunctions(dqmcb_ctx* ctx) {
         ctx->err = "init_greenfunctions before init_stacks";
         return DQMCB_ESTATE;
     }
+    TimeScope ts(ctx, DQMCB_K_INIT);
     k_init_green<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p);
     CK(cudaGetLastError());
     ctx->green_ready = true;
@@ -750,6 +808,7 @@ int dqmcb_get_block_product(dqmcb_ctx* ctx, double* out) {
     return DQMCB_OK;
 }
 static int launch_stabilize(dqmcb_ctx* ctx, int l, int dir) {
+    TimeScope ts(ctx, DQMCB_K_STABILIZE);
     k_stabilize<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p, l, dir);
     CK(cudaGetLastError());
     return DQMCB_OK;
@@ -891,7 +950,10 @@ void* dqmcb_device_ptr(dqmcb_ctx* ctx, int which) {
 int dqmcb_measure_equal_time(dqmcb_ctx* ctx, double* scalars, double* corr) {
     NEED(ctx);
     const Params& p = ctx->p;
-    k_measure<<<p.W, kThreads, 0, ctx->stream>>>(p, ctx->d_obs, corr ? ctx->d_scratchNN : nullptr);
+    {
+        TimeScope ts(ctx, DQMCB_K_OTHER);
+        k_measure<<<p.W, kThreads, 0, ctx->stream>>>(p, ctx->d_obs, corr ? ctx->d_scratchNN : nullptr);
+    }
     CK(cudaGetLastError());
     CK(cudaStreamSynchronize(ctx->stream));
     std::vector<double> o((size_t)p.W * 4);
@@ -939,6 +1001,7 @@ int dqmcb_run_sweeps_host(dqmcb_ctx* ctx, int reinit, const int8_t* fields_in, i
         if (int rc = dqmcb_sweep_beta_to_0(ctx)) return rc;
     }
     if (scalars_out) {
+        TimeScope ts(ctx, DQMCB_K_OTHER);
         k_measure<<<p.W, kThreads, 0, ctx->stream>>>(p, ctx->d_obs, nullptr);
         CK(cudaGetLastError());
     }

@@ -4,6 +4,7 @@
 #include <stdint.h>
 
 #include <string>
+#include <vector>
 
 #include "../../include/dqmc_b200.h"
 
@@ -69,4 +70,10 @@ struct dqmcb_ctx {
     double* d_scratchNN = nullptr;  // [W][N*N] for measurement outputs
     uint32_t* d_mt = nullptr;       // [W][625] mt19937 state + index (MT19937 mode)
     size_t smem_prop = 0, smem_stab = 0;
+    // optional per-launch timing
+    bool timing = false;
+    struct Span { cudaEvent_t a, b; int cls; };
+    std::vector<Span> spans;
+    double t_ms[DQMCB_K_CLASSES] = {0, 0, 0, 0};
+    long long t_n[DQMCB_K_CLASSES] = {0, 0, 0, 0};
 };

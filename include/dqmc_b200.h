@@ -145,6 +145,15 @@ int dqmcb_inv_I_plus_ldr(int device, int n, int batch, const double* L, const do
 int dqmcb_inv_I_plus_ldr_mul_ldr(int device, int n, int batch, const double* L1, const double* d1, const double* R1,
                                  const double* L2, const double* d2, const double* R2, double* G);
 
+/* ---- per-kernel-class device timing (CUDA events on the context's stream), for bench.py's roofline ---- */
+#define DQMCB_K_PROPAGATE 0 /* wrap + Metropolis kernels */
+#define DQMCB_K_STABILIZE 1 /* Bbar + stack update + stabilised G kernels */
+#define DQMCB_K_INIT 2      /* init_stacks / init_greenfunctions */
+#define DQMCB_K_OTHER 3     /* measurement, action, half wrap */
+#define DQMCB_K_CLASSES 4
+int dqmcb_timing_enable(dqmcb_ctx* ctx, int on); /* turning it on resets the counters */
+int dqmcb_timing_get(dqmcb_ctx* ctx, double* ms /* [4] */, long long* launches /* [4] */);
+
 /* update::partner_rank, source/update.cpp:34-45 (pure host arithmetic) */
 int dqmcb_partner_rank(int rank, int world_size, int exchange_attempt);
 

@@ -6,6 +6,7 @@
 #include <math.h>
 #include <stdio.h>
 #include <string.h>
+#include <stdlib.h>
 
 #include <algorithm>
 #include <string>
@@ -551,6 +552,7 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
     CKC(cudaFuncSetAttribute(k_init_stacks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
     CKC(cudaFuncSetAttribute(k_init_green, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
     CKC(cudaFuncSetAttribute(k_ldr_op, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
+    { const char* fg = getenv("DQMCB_FORCE_GENERIC"); ctx->force_generic = fg && fg[0] == (char)49; }
     CKC(fast64_setup(ctx));
 #undef CKC
     *out = ctx;
@@ -752,7 +754,7 @@ static int launch_propagate(dqmcb_ctx* ctx, int l_first, int n_slices, int dir, 
 int dqmcb_init_stacks(dqmcb_ctx* ctx) {
     NEED(ctx);
     TimeScope ts(ctx, DQMCB_K_INIT);
-    k_init_stacks<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p);
+    if (fast64_available(ctx)) fast_init_stacks(ctx); else k_init_stacks<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p);
     CK(cudaGetLastError());
     ctx->stacks_ready = true;
     return DQMCB_OK;
@@ -764,7 +766,7 @@ int dqmcb_init_greenfunctions(dqmcb_ctx* ctx) {
         return DQMCB_ESTATE;
     }
     TimeScope ts(ctx, DQMCB_K_INIT);
-    k_init_green<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p);
+    if (fast64_available(ctx)) fast_init_green(ctx); else k_init_green<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p);
     CK(cudaGetLastError());
     ctx->green_ready = true;
     return DQMCB_OK;
@@ -797,7 +799,7 @@ int dqmcb_block_product(dqmcb_ctx* ctx, int i_stack) {
         ctx->err = "LDR Stack index out of bounds";
         return DQMCB_EINVAL;
     }
-    k_bbar<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p, i_stack);
+    if (fast64_available(ctx)) fast_bbar(ctx, i_stack); else k_bbar<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p, i_stack);
     CK(cudaGetLastError());
     return DQMCB_OK;
 }
@@ -809,7 +811,7 @@ int dqmcb_get_block_product(dqmcb_ctx* ctx, double* out) {
 }
 static int launch_stabilize(dqmcb_ctx* ctx, int l, int dir) {
     TimeScope ts(ctx, DQMCB_K_STABILIZE);
-    k_stabilize<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p, l, dir);
+    if (fast64_available(ctx)) fast_stabilize(ctx, l, dir); else k_stabilize<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p, l, dir);
     CK(cudaGetLastError());
     return DQMCB_OK;
 }

@@ -71,6 +71,7 @@ struct dqmcb_ctx {
     uint32_t* d_mt = nullptr;       // [W][625] mt19937 state + index (MT19937 mode)
     size_t smem_prop = 0, smem_stab = 0;
     // optional per-launch timing
+    bool force_generic = false;  // DQMCB_FORCE_GENERIC=1: bypass the compile-time-N fast path (parity cross-checks)
     bool timing = false;
     struct Span { cudaEvent_t a, b; int cls; };
     std::vector<Span> spans;

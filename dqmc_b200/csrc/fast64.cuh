@@ -1,7 +1,403 @@
-// fast64.cuh -- N = 64 fast path (placeholder until the DMMA / register-resident kernels land).
+// fast64.cuh -- compile-time-N fast path of the sweep engine (N = 32 or 64; the headline config
+// C1 is N = 64).  Same mathematics and operation order as engine.cuh (which remains the any-N path
+// and the second parity reference), but
+//   * every dense product runs on the FP64 tensor cores (mma.sync m8n8k4 f64 -> DMMA.8x8x4) from
+//     bank-conflict-free shared-memory tiles (tile.cuh),
+//   * HBM operands written by earlier kernels are staged with TMA bulk copies (cp.async.bulk),
+//   * QR / LU / triangular solves are fully unrolled for N,
+//   * the propagate kernel keeps G in registers (DMMA accumulator layout) across wrap and flips,
+//     batches several walkers per CTA so exp(-+dtau K) is shared in SMEM, and emits the block
+//     product Bbar as a tail phase.
 #pragma once
 #include "dqmcb_internal.cuh"
+#include "engine.cuh"
+#include "tile.cuh"
 
-static inline cudaError_t fast64_setup(dqmcb_ctx*) { return cudaSuccess; }
-static inline bool fast64_available(const dqmcb_ctx*) { return false; }
-static inline int fast64_propagate(dqmcb_ctx*, const dq::Params&, int, int, int, unsigned long long, int) { return DQMCB_ESTATE; }
+namespace dq {
+
+// ---------------------------------------------------------------------------------------------------
+// shared-memory plan of the stabilisation kernels: small vectors, 2 mbarriers, 3 tiles
+// ---------------------------------------------------------------------------------------------------
+template <int N>
+struct StabSmem {
+    static constexpr size_t SMALL = ((size_t)(10 * N + 64) * 8 + (size_t)(2 * N + 4) * 4 + 15) & ~(size_t)15;
+    static constexpr size_t BARS = 16;
+    static constexpr size_t TOTAL = SMALL + BARS + 3 * Tile<N>::BYTES;
+};
+
+template <int N>
+struct FWork {
+    double* t[3];
+    double *tau, *vn1, *vn2, *sv[4], *dnew, *prow, *jrow, *red;
+    int *jpvt, *ipiv, *info;
+    uint64_t* bar;
+    uint32_t parity;
+};
+
+template <int N>
+__device__ inline void fcarve(FWork<N>& wk, unsigned char* smem) {
+    double* s = reinterpret_cast<double*>(smem);
+    wk.tau = s;
+    wk.vn1 = s + N;
+    wk.vn2 = s + 2 * N;
+    for (int i = 0; i < 4; ++i) wk.sv[i] = s + (3 + i) * N;
+    wk.dnew = s + 7 * N;
+    wk.prow = s + 8 * N;
+    wk.jrow = s + 9 * N;
+    wk.red = s + 10 * N;
+    int* ip = reinterpret_cast<int*>(s + 10 * N + 64);
+    wk.jpvt = ip;
+    wk.ipiv = ip + N;
+    wk.info = ip + 2 * N;
+    wk.bar = reinterpret_cast<uint64_t*>(smem + StabSmem<N>::SMALL);
+    double* tiles = reinterpret_cast<double*>(smem + StabSmem<N>::SMALL + StabSmem<N>::BARS);
+    for (int i = 0; i < 3; ++i) wk.t[i] = tiles + (size_t)i * Tile<N>::ELEMS;
+    wk.parity = 0;
+    if (threadIdx.x == 0) {
+        mbar_init(wk.bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+        fence_proxy_async();
+    }
+    __syncthreads();
+}
+
+// Blocking TMA fetch of a dense global N x N matrix (written by an EARLIER kernel) into a tile.
+template <int N>
+__device__ inline void tile_fetch(FWork<N>& wk, double* dst, const double* __restrict__ src) {
+    fence_proxy_async();  // order this thread's earlier generic accesses to `dst` before the async writes
+    tile_load_async<N>(dst, src, wk.bar);
+    mbar_wait(wk.bar, wk.parity);
+    wk.parity ^= 1;
+}
+
+// to_LDR on tile A (destroyed): Q -> tile Qo, D^-1 R P^T -> tile Ro, |diag R| -> dout
+template <int N>
+__device__ void f_to_ldr(FWork<N>& wk, double* A, double* Qo, double* Ro, double* dout) {
+    constexpr int LDT = Tile<N>::LDT;
+    __syncthreads();
+    qrp_tile<N>(A, wk.tau, wk.jpvt, wk.vn1, wk.vn2);
+    for (int j = threadIdx.x; j < N; j += blockDim.x) {
+        const double dj = fabs(A[j + (size_t)j * LDT]);
+        dout[j] = dj;
+        wk.vn1[j] = 1.0 / dj;
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < N * N; e += blockDim.x) {
+        const int i = e % N, j = e / N;
+        const double v = (i <= j) ? wk.vn1[i] * A[i + (size_t)j * LDT] : 0.0;
+        Ro[i + (size_t)wk.jpvt[j] * LDT] = v;
+    }
+    form_q_tile<N>(Qo, A, wk.tau);
+    __syncthreads();
+}
+
+template <int N>
+__device__ inline void f_set_diag(double* B, const double* dvec) {
+    constexpr int LDT = Tile<N>::LDT;
+    for (int e = threadIdx.x; e < N * N; e += blockDim.x) {
+        const int r = e % N, c = e / N;
+        B[r + (size_t)c * LDT] = (r == c) ? dvec[r] : 0.0;
+    }
+}
+
+template <int N>
+__device__ inline void f_note_fail(const Params& p, const FWork<N>& wk, int code) {
+    if (threadIdx.x == 0 && *wk.info != 0) atomicCAS(p.fail, 0, code);
+}
+
+// inv_I_plus_ldr (source/stablelinalg.cpp:94-126); L, d, R dense global (ld = N).  G -> wk.t[2].
+template <int N>
+__device__ double f_inv_I_plus_ldr(const Params& p, FWork<N>& wk, const double* L, const double* d, const double* R) {
+    constexpr int LDT = Tile<N>::LDT;
+    double *t0 = wk.t[0], *t1 = wk.t[1], *t2 = wk.t[2];
+    __syncthreads();
+    split_d(d, N, wk.sv[0], wk.sv[1]);
+    tile_load_global<N>(t1, R);
+    double part = 0.0;
+    for (int i = threadIdx.x; i < N; i += blockDim.x) part += (d[i] >= 1.0) ? log(d[i]) : 0.0;
+    const double logdl = cta_reduce_sum(part, wk.red);  // contains barriers
+    lu_tile<N>(t1, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    f_note_fail<N>(p, wk, 10);
+    f_set_diag<N>(t2, wk.sv[0]);
+    __syncthreads();
+    lu_solve_tile<N>(t1, wk.ipiv, t2, 1, LDT);  // X
+    __syncthreads();
+    for (int e = threadIdx.x; e < N * N; e += blockDim.x) {  // t0 <- M^T,  M = X + L D_small
+        const int r = e % N, c = e / N;
+        t0[c + (size_t)r * LDT] = t2[r + (size_t)c * LDT] + L[r + (size_t)c * N] * wk.sv[1][c];
+    }
+    __syncthreads();
+    lu_tile<N>(t0, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    f_note_fail<N>(p, wk, 11);
+    part = 0.0;
+    for (int i = threadIdx.x; i < N; i += blockDim.x) part += log(fabs(t0[i + (size_t)i * LDT]));
+    const double logm = cta_reduce_sum(part, wk.red);
+    lu_solve_tile<N>(t0, wk.ipiv, t2, LDT, 1);  // M^T Gt = X^T, in place on X viewed transposed
+    __syncthreads();
+    return logdl + logm;
+}
+
+// inv_I_plus_ldr_mul_ldr (source/stablelinalg.cpp:128-158); all six inputs dense global (ld = N).
+// G -> wk.t[2].
+template <int N>
+__device__ void f_inv_I_plus_ldr_mul_ldr(const Params& p, FWork<N>& wk, const double* L1, const double* d1, const double* R1,
+                                         const double* L2, const double* d2, const double* R2) {
+    constexpr int LDT = Tile<N>::LDT;
+    double *t0 = wk.t[0], *t1 = wk.t[1], *t2 = wk.t[2];
+    __syncthreads();
+    split_d(d1, N, wk.sv[0], wk.sv[1]);
+    split_d(d2, N, wk.sv[2], wk.sv[3]);
+    tile_load_global<N>(t0, R2);
+    __syncthreads();
+    lu_tile<N>(t0, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    f_note_fail<N>(p, wk, 12);
+    f_set_diag<N>(t1, wk.sv[2]);
+    __syncthreads();
+    lu_solve_tile<N>(t0, wk.ipiv, t1, 1, LDT);  // X = R2^-1 D2l^-1  (t1)
+    __syncthreads();
+    // M = D1l^-1 (L1^T X) + D1s (R1 (L2 D2s))   (t2).  The column scaling by D2s is applied to the
+    // product instead of to L2 first: identical in exact arithmetic, no cancellation involved.
+    cta_mma<N, false>(t2, LDT, L1, N, 1, t1, 1, LDT, wk.sv[0], nullptr);
+    __syncthreads();
+    cta_mma<N, true>(t2, LDT, R1, 1, N, L2, 1, N, wk.sv[1], wk.sv[3]);
+    // RHS = D1l^-1 L1^T  (t0; the LU of R2 is dead)
+    for (int e = threadIdx.x; e < N * N; e += blockDim.x) {
+        const int c = e % N, r = e / N;
+        t0[r + (size_t)c * LDT] = wk.sv[0][r] * L1[c + (size_t)r * N];
+    }
+    __syncthreads();
+    lu_tile<N>(t2, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    f_note_fail<N>(p, wk, 13);
+    lu_solve_tile<N>(t2, wk.ipiv, t0, 1, LDT);  // Y (t0)
+    __syncthreads();
+    cta_mma<N, false>(t2, LDT, t1, 1, LDT, t0, 1, LDT, nullptr, nullptr);  // G = X Y
+    __syncthreads();
+}
+
+}  // namespace dq
+
+namespace dq {
+
+// calculate_Bbar (source/dqmc.cpp:88-105) on the tensor cores: expK staged once into t[2], running
+// product ping-pongs between t[0] and t[1]; result in t[0].
+template <int N>
+__device__ void f_bbar(const Params& p, FWork<N>& wk, int walker, int i_stack) {
+    constexpr int LDT = Tile<N>::LDT;
+    const int l0 = i_stack * p.n_stab;
+    const int l1 = min(l0 + p.n_stab, p.nt);
+    const int8_t* f = p.fields + ((size_t)walker * p.nt) * N;
+    const int m = l1 - l0;
+    double* cur = (m & 1) ? wk.t[0] : wk.t[1];
+    double* oth = (m & 1) ? wk.t[1] : wk.t[0];
+    __syncthreads();
+    tile_fetch<N>(wk, wk.t[2], p.expK);
+    for (int i = threadIdx.x; i < N; i += blockDim.x) wk.sv[0][i] = p.lut_ev[f[(size_t)l0 * N + i]];
+    __syncthreads();
+    for (int e = threadIdx.x; e < N * N; e += blockDim.x) {
+        const int r = e % N, c = e / N;
+        cur[r + (size_t)c * LDT] = wk.sv[0][r] * wk.t[2][r + (size_t)c * LDT];
+    }
+    __syncthreads();
+    for (int l = l0 + 1; l < l1; ++l) {
+        for (int i = threadIdx.x; i < N; i += blockDim.x) wk.sv[0][i] = p.lut_ev[f[(size_t)l * N + i]];
+        __syncthreads();
+        cta_mma<N, false>(oth, LDT, wk.t[2], 1, LDT, cur, 1, LDT, wk.sv[0], nullptr);
+        __syncthreads();
+        double* tmp = cur;
+        cur = oth;
+        oth = tmp;
+    }
+}
+
+__device__ inline double* fstkL(const Params& p, int w, int i) { return p.stackL + ((size_t)w * p.n_stack + i) * p.N * p.N; }
+__device__ inline double* fstkR(const Params& p, int w, int i) { return p.stackR + ((size_t)w * p.n_stack + i) * p.N * p.N; }
+__device__ inline double* fstkD(const Params& p, int w, int i) { return p.stackD + ((size_t)w * p.n_stack + i) * p.N; }
+__device__ inline void fstore_d(double* dst, const double* src, int n) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
+}
+
+template <int N>
+__global__ void __launch_bounds__(kThreads, 2) kf_bbar(Params p, int i_stack) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    FWork<N> wk;
+    fcarve<N>(wk, smem);
+    f_bbar<N>(p, wk, blockIdx.x, i_stack);
+    __syncthreads();
+    tile_store_global<N>(p.Bbar + (size_t)blockIdx.x * N * N, wk.t[0]);
+}
+
+// End-of-block work (source/dqmc.cpp:369-394 / 429-454), fast path.  Same structure as k_stabilize.
+template <int N>
+__global__ void __launch_bounds__(kThreads, 2) kf_stabilize(Params p, int l, int dir) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    constexpr int LDT = Tile<N>::LDT;
+    const int w = blockIdx.x;
+    FWork<N> wk;
+    fcarve<N>(wk, smem);
+    const int i = l / p.n_stab;
+    f_bbar<N>(p, wk, w, i);  // -> t[0]
+    double *t0 = wk.t[0], *t1 = wk.t[1], *t2 = wk.t[2];
+    __syncthreads();
+    const bool first = (dir > 0) ? (i == 0) : (i == p.n_stack - 1);
+    if (first) {
+        f_to_ldr<N>(wk, t0, t1, t2, wk.dnew);
+        tile_store_global<N>(fstkL(p, w, i), t1);
+        tile_store_global<N>(fstkR(p, w, i), t2);
+    } else if (dir > 0) {
+        // mat_mul_ldr: (Bbar L_prev) D_prev -> QR ; R <- R_new R_prev
+        fstore_d(wk.sv[0], fstkD(p, w, i - 1), N);
+        tile_fetch<N>(wk, t1, fstkL(p, w, i - 1));
+        __syncthreads();
+        cta_mma<N, false>(t2, LDT, t0, 1, LDT, t1, 1, LDT, nullptr, wk.sv[0]);
+        f_to_ldr<N>(wk, t2, t0, t1, wk.dnew);
+        tile_store_global<N>(fstkL(p, w, i), t0);
+        tile_fetch<N>(wk, t2, fstkR(p, w, i - 1));
+        __syncthreads();
+        cta_mma<N, false>(fstkR(p, w, i), N, t1, 1, LDT, t2, 1, LDT, nullptr, nullptr);
+    } else {
+        // ldr_mul_mat: D_next (R_next Bbar) -> QR ; L <- L_next Q
+        fstore_d(wk.sv[0], fstkD(p, w, i + 1), N);
+        tile_fetch<N>(wk, t1, fstkR(p, w, i + 1));
+        __syncthreads();
+        cta_mma<N, false>(t2, LDT, t1, 1, LDT, t0, 1, LDT, wk.sv[0], nullptr);
+        f_to_ldr<N>(wk, t2, t0, t1, wk.dnew);
+        tile_store_global<N>(fstkR(p, w, i), t1);
+        tile_fetch<N>(wk, t2, fstkL(p, w, i + 1));
+        __syncthreads();
+        cta_mma<N, false>(fstkL(p, w, i), N, t2, 1, LDT, t0, 1, LDT, nullptr, nullptr);
+    }
+    fstore_d(fstkD(p, w, i), wk.dnew, N);
+    __syncthreads();
+    const bool at_end = (dir > 0) ? (l == p.nt - 1) : (l == 0);
+    if (at_end) {
+        const double ld_ = f_inv_I_plus_ldr<N>(p, wk, fstkL(p, w, i), fstkD(p, w, i), fstkR(p, w, i));
+        if (threadIdx.x == 0) p.logdet[w] = ld_;
+    } else if (dir > 0) {
+        f_inv_I_plus_ldr_mul_ldr<N>(p, wk, fstkL(p, w, i), fstkD(p, w, i), fstkR(p, w, i), fstkL(p, w, i + 1), fstkD(p, w, i + 1),
+                                    fstkR(p, w, i + 1));
+    } else {
+        f_inv_I_plus_ldr_mul_ldr<N>(p, wk, fstkL(p, w, i - 1), fstkD(p, w, i - 1), fstkR(p, w, i - 1), fstkL(p, w, i), fstkD(p, w, i),
+                                    fstkR(p, w, i));
+    }
+    // check_error + install
+    double* Gg = p.G + (size_t)w * N * N;
+    double emax = 0.0;
+    for (int e = threadIdx.x; e < N * N; e += blockDim.x) {
+        const int r = e % N, c = e / N;
+        const double v = t2[r + (size_t)c * LDT];
+        emax = fmax(emax, fabs(Gg[e] - v));
+        Gg[e] = v;
+    }
+    emax = cta_reduce_max(emax, wk.red);
+    if (threadIdx.x == 0) {
+        p.err_max[w] = fmax(p.err_max[w], emax);
+        p.err_sum[w] += emax;
+        p.err_cnt[w] += 1ull;
+    }
+}
+
+// init_stacks (source/dqmc.cpp:43-59), fast path
+template <int N>
+__global__ void __launch_bounds__(kThreads, 2) kf_init_stacks(Params p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    constexpr int LDT = Tile<N>::LDT;
+    const int w = blockIdx.x;
+    FWork<N> wk;
+    fcarve<N>(wk, smem);
+    double *t0 = wk.t[0], *t1 = wk.t[1], *t2 = wk.t[2];
+    for (int i = p.n_stack - 1; i >= 0; --i) {
+        f_bbar<N>(p, wk, w, i);
+        __syncthreads();
+        f_to_ldr<N>(wk, t0, t1, t2, wk.sv[2]);  // Bbar_ldr: L2 = t1, R2 = t2, d2 = sv[2]
+        if (i == p.n_stack - 1) {
+            tile_store_global<N>(fstkL(p, w, i), t1);
+            tile_store_global<N>(fstkR(p, w, i), t2);
+            fstore_d(fstkD(p, w, i), wk.sv[2], N);
+        } else {
+            // ldr_mul_ldr(stack[i+1], Bbar_ldr): M' = D1 (R1 L2) D2 -> QR ; L = L1 Q ; R = R_new R2
+            fstore_d(wk.sv[0], fstkD(p, w, i + 1), N);
+            __syncthreads();
+            cta_mma<N, false>(t0, LDT, fstkR(p, w, i + 1), 1, N, t1, 1, LDT, wk.sv[0], wk.sv[2]);
+            // park R2 in the (not yet written) global R slot of entry i while the tiles are busy
+            tile_store_global<N>(fstkR(p, w, i), t2);
+            f_to_ldr<N>(wk, t0, t1, t2, wk.dnew);  // Q = t1, R_new = t2
+            cta_mma<N, false>(fstkL(p, w, i), N, fstkL(p, w, i + 1), 1, N, t1, 1, LDT, nullptr, nullptr);
+            tile_load_global<N>(t0, fstkR(p, w, i));  // R2 back (same CTA wrote it: generic proxy)
+            __syncthreads();
+            cta_mma<N, false>(fstkR(p, w, i), N, t2, 1, LDT, t0, 1, LDT, nullptr, nullptr);
+            fstore_d(fstkD(p, w, i), wk.dnew, N);
+        }
+        __syncthreads();
+    }
+}
+
+template <int N>
+__global__ void __launch_bounds__(kThreads, 2) kf_init_green(Params p) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int w = blockIdx.x;
+    FWork<N> wk;
+    fcarve<N>(wk, smem);
+    const double ld_ = f_inv_I_plus_ldr<N>(p, wk, fstkL(p, w, 0), fstkD(p, w, 0), fstkR(p, w, 0));
+    if (threadIdx.x == 0) p.logdet[w] = ld_;
+    tile_store_global<N>(p.G + (size_t)w * N * N, wk.t[2]);
+}
+
+}  // namespace dq
+
+#include "prop64.cuh"
+
+// =====================================================================================================
+// host-side dispatch of the fast path
+// =====================================================================================================
+static inline bool fast_n(int n) { return n == 64 || n == 32; }
+static inline bool fast64_available(const dqmcb_ctx* ctx) { return fast_n(ctx->p.N) && !ctx->force_generic; }
+
+#define FAST_DISPATCH(N_, EXPR)             \
+    do {                                    \
+        if ((N_) == 64) {                   \
+            constexpr int FN = 64;          \
+            EXPR;                           \
+        } else {                            \
+            constexpr int FN = 32;          \
+            EXPR;                           \
+        }                                   \
+    } while (0)
+
+template <int N>
+static cudaError_t fast_setup_n() {
+    cudaError_t e;
+    const int sm = (int)dq::StabSmem<N>::TOTAL;
+    if ((e = cudaFuncSetAttribute(dq::kf_bbar<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(dq::kf_stabilize<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(dq::kf_init_stacks<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(dq::kf_init_green<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm)) != cudaSuccess) return e;
+    return dq::fast_prop_setup<N>();
+}
+
+static inline cudaError_t fast64_setup(dqmcb_ctx* ctx) {
+    if (!fast_n(ctx->p.N)) return cudaSuccess;
+    cudaError_t e = cudaSuccess;
+    FAST_DISPATCH(ctx->p.N, e = fast_setup_n<FN>());
+    return e;
+}
+
+static inline void fast_bbar(dqmcb_ctx* ctx, int i_stack) {
+    const dq::Params& p = ctx->p;
+    FAST_DISPATCH(p.N, (dq::kf_bbar<FN><<<p.W, dq::kThreads, dq::StabSmem<FN>::TOTAL, ctx->stream>>>(p, i_stack)));
+}
+static inline void fast_stabilize(dqmcb_ctx* ctx, int l, int dir) {
+    const dq::Params& p = ctx->p;
+    FAST_DISPATCH(p.N, (dq::kf_stabilize<FN><<<p.W, dq::kThreads, dq::StabSmem<FN>::TOTAL, ctx->stream>>>(p, l, dir)));
+}
+static inline void fast_init_stacks(dqmcb_ctx* ctx) {
+    const dq::Params& p = ctx->p;
+    FAST_DISPATCH(p.N, (dq::kf_init_stacks<FN><<<p.W, dq::kThreads, dq::StabSmem<FN>::TOTAL, ctx->stream>>>(p)));
+}
+static inline void fast_init_green(dqmcb_ctx* ctx) {
+    const dq::Params& p = ctx->p;
+    FAST_DISPATCH(p.N, (dq::kf_init_green<FN><<<p.W, dq::kThreads, dq::StabSmem<FN>::TOTAL, ctx->stream>>>(p)));
+}
+static inline int fast64_propagate(dqmcb_ctx* ctx, const dq::Params& p, int l_first, int n_slices, int dir, unsigned long long v0, int flags) {
+    FAST_DISPATCH(p.N, dq::fast_prop_launch<FN>(ctx, p, l_first, n_slices, dir, v0, flags));
+    return cudaGetLastError() == cudaSuccess ? DQMCB_OK : DQMCB_ECUDA;
+}

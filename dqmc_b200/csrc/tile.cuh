@@ -55,6 +55,35 @@ __device__ __forceinline__ void warp_mma(double (&acc)[MB][NB][2], const double*
     }
 }
 
+// Same product restricted to the n-blocks [NB0, NB0 + NBC) of a wider accumulator array (keeps the
+// B-fragment double buffer small when a warp owns a wide tile).
+template <int MB, int NBTOT, int NB0, int NBC, int K>
+__device__ __forceinline__ void warp_mma_cols(double (&acc)[MB][NBTOT][2], const double* __restrict__ A, int rsA, int csA,
+                                              const double* __restrict__ B, int rsB, int csB, int r0) {
+    const int lane = threadIdx.x & 31, gr = lane >> 2, tg = lane & 3;
+    const double* ap = A + (size_t)(r0 + gr) * rsA + (size_t)tg * csA;
+    const double* bp = B + (size_t)tg * rsB + (size_t)(8 * NB0 + gr) * csB;
+    double a[2][MB], b[2][NBC];
+#pragma unroll
+    for (int m = 0; m < MB; ++m) a[0][m] = ap[(size_t)(8 * m) * rsA];
+#pragma unroll
+    for (int n = 0; n < NBC; ++n) b[0][n] = bp[(size_t)(8 * n) * csB];
+#pragma unroll
+    for (int k0 = 0; k0 < K; k0 += 4) {
+        const int cur = (k0 >> 2) & 1, nxt = cur ^ 1;
+        if (k0 + 4 < K) {
+#pragma unroll
+            for (int m = 0; m < MB; ++m) a[nxt][m] = ap[(size_t)(8 * m) * rsA + (size_t)(k0 + 4) * csA];
+#pragma unroll
+            for (int n = 0; n < NBC; ++n) b[nxt][n] = bp[(size_t)(k0 + 4) * rsB + (size_t)(8 * n) * csB];
+        }
+#pragma unroll
+        for (int m = 0; m < MB; ++m)
+#pragma unroll
+            for (int n = 0; n < NBC; ++n) dmma884(acc[m][NB0 + n][0], acc[m][NB0 + n][1], a[cur][m], b[cur][n]);
+    }
+}
+
 template <int MB, int NB>
 __device__ __forceinline__ void acc_zero(double (&acc)[MB][NB][2]) {
 #pragma unroll

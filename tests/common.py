@@ -10,6 +10,7 @@ CONFIGS = {
     "C1s": (8, 8, 4.0, 1.0, 0.0, 2.0, 20, 5),      # short 8x8 case for quick checks
     "C2s": (12, 12, 4.0, 1.0, 0.0, 2.0, 20, 5),    # 12x12, global-workspace path
     "R7": (7, 5, 3.0, 1.0, 0.2, 3.0, 23, 6),       # odd N, ragged last block (nt % n_stab != 0)
+    "F32": (8, 4, 5.0, 1.0, 0.1, 2.3, 23, 5),      # N = 32 fast path, ragged last block
 }
 
 

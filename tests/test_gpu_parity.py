@@ -26,7 +26,7 @@ def _setup(name, seeds):
     return cfg, pairs, ctx
 
 
-@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "C2s"])
+@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "C2s", "F32"])
 def test_init_stacks_and_green(name):
     cfg, pairs, ctx = _setup(name, [11, 12, 13])
     ctx.init_stacks()
@@ -48,7 +48,7 @@ def test_init_stacks_and_green(name):
             assert np.allclose(Lm[w].T @ Lm[w], np.eye(m.ns), atol=1e-12)
 
 
-@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "C2s"])
+@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "C2s", "F32"])
 def test_wrap_steps_teacher_forced(name):
     cfg, pairs, ctx = _setup(name, [21, 22])
     rng = np.random.default_rng(5)
@@ -66,7 +66,7 @@ def test_wrap_steps_teacher_forced(name):
             assert rel_err(Gb[w], d.wrap_backward(G0[w], l)) < TOL
 
 
-@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "C2s"])
+@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "C2s", "F32"])
 def test_block_product(name):
     cfg, pairs, ctx = _setup(name, [31, 32])
     for i in range(ctx.n_stack):
@@ -75,7 +75,7 @@ def test_block_product(name):
             assert rel_err(B[w], d.calculate_Bbar(i)) < TOL
 
 
-@pytest.mark.parametrize("name", ["C0", "C1s", "R7"])
+@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "F32"])
 def test_local_update_teacher_forced(name):
     """One slice of Metropolis from the oracle's G: identical decisions and fields, G to 1e-10."""
     cfg, pairs, ctx = _setup(name, [41, 42, 43])
@@ -102,7 +102,7 @@ def test_local_update_teacher_forced(name):
         G_prev = G
 
 
-@pytest.mark.parametrize("name,n_sweeps", [("C0", 3), ("C1s", 3), ("R7", 3), ("C2s", 1)])
+@pytest.mark.parametrize("name,n_sweeps", [("C0", 3), ("C1s", 3), ("R7", 3), ("C2s", 1), ("F32", 3), ("C1", 1)])
 def test_trajectory(name, n_sweeps):
     """Free-running sweeps on the same RNG tape: identical accept decisions / fields; G compared at
     the end of each half sweep (a stabilisation point, where G is a function of the fields only)."""

@@ -50,6 +50,8 @@ def lib():
             getattr(L, name).restype = C.c_double
             getattr(L, name).argtypes = [C.c_void_p]
         L.ref_local_update.restype = C.c_double
+        L.ref_rng_peek_canonical.restype = C.c_double
+        L.ref_rng_peek_canonical.argtypes = [C.c_void_p]
         L.ref_local_update.argtypes = [C.c_void_p, C.c_int]
         L.ref_inv_I_plus_ldr.restype = C.c_double
         L.ref_run_sweeps.restype = C.c_double
@@ -221,6 +223,10 @@ class RefSim:
 
     def mean_err(self):
         return self.L.ref_mean_err(self.h)
+
+    def peek_canonical(self) -> float:
+        """u of the next rng.bernoulli() call (replica-exchange decider), generator not advanced."""
+        return self.L.ref_rng_peek_canonical(self.h)
 
     def rng_tape(self, n_calls: int, advance: bool = False):
         """(perm, k, u), each [n_calls, N]: the draws the next n_calls local_update calls make."""

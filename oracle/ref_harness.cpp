@@ -255,6 +255,12 @@ void ref_rng_tape(void* h, int n_calls, int advance, int* perm, int* k, double* 
     }
     if (advance) s->rng->get_generator() = g;
 }
+// the canonical double the NEXT rng.bernoulli() call would compare with p (include/utility.h:34-37),
+// without advancing the generator (replica-exchange decider, source/update.cpp:96)
+double ref_rng_peek_canonical(void* h) {
+    std::mt19937 g = ((Sim*)h)->rng->get_generator();
+    return std::generate_canonical<double, std::numeric_limits<double>::digits>(g);
+}
 // raw 32-bit outputs of a fresh mt19937(seed) (for testing device-side generators)
 void ref_mt19937_raw(unsigned seed, int n, unsigned* out) {
     std::mt19937 g(seed);

@@ -17,3 +17,15 @@ def have_ref():
     from oracle import ref
 
     return ref.available()
+
+
+def pytest_sessionstart(session):
+    """Build the in-tree native artefacts if they are missing (nvcc cross-compiles without a GPU)."""
+    lib = os.path.join(ROOT, "dqmc_b200", "libdqmc_b200.so")
+    if not os.path.exists(lib):
+        import shutil
+
+        if shutil.which("nvcc"):
+            import __graft_entry__ as g
+
+            g.build()

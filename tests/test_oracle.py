@@ -1,0 +1,264 @@
+"""Pins the CPU oracle (oracle/dqmc_oracle.py) against outputs of the reference itself.
+
+The reference ships no tests or golden vectors.  The fixtures under
+tests/golden/ were produced by tests/golden/make_golden.py from the reference's own sources compiled
+unmodified (oracle/_ref); these tests need only the committed .npz files.  When oracle/_ref is
+present (build container, and the GPU box via the prebuilt .so) a few live cross-checks run too.
+
+Tolerances: integer / decision data bit-exact; floating point 1e-10 relative (north_star), looser
+only where stated (free-running wrapped G: the reference's own drift envelope).
+"""
+import math
+import os
+
+import numpy as np
+import pytest
+
+from oracle import dqmc_oracle as O
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+TOL = 1e-10
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
+
+
+def load(name):
+    return np.load(os.path.join(GOLD, name))
+
+
+def build_from_gold(g):
+    L1, L2, U, t, mu, beta, nt, n_stab, seed, n_sweeps = g["cfg"]
+    L1, L2, nt, n_stab, seed, n_sweeps = int(L1), int(L2), int(nt), int(n_stab), int(seed), int(n_sweeps)
+    f = O.random_fields(seed, nt, L1 * L2)
+    m = O.Model(L1, L2, U, t, mu, beta, nt, fields=f)
+    d = O.DQMC(m, n_stab)
+    return m, d, seed, n_sweeps
+
+
+def test_mt19937_and_partner_rank():
+    g = load("misc.npz")
+    for seed, key in ((5489, "mt19937_seed5489"), (1, "mt19937_seed1")):
+        gen = O.MT19937(seed)
+        assert [gen.next() for _ in range(16)] == [int(x) for x in g[key]]
+    tab = g["partner_rank_ws248_r8_a1to4"]
+    for wi, ws in enumerate((2, 4, 8)):
+        for r in range(ws):
+            for ai, a in enumerate(range(1, 5)):
+                assert O.partner_rank(r, ws, a) == tab[wi, r, ai]
+
+
+@pytest.mark.parametrize("name", ["c0", "r7", "c1s"])
+def test_model_and_init(name):
+    g = load(f"traj_{name}.npz")
+    m, d, seed, _ = build_from_gold(g)
+    assert np.array_equal(m.fields, g["fields0"])  # GHQField ctor draw order (include/field.h:52-57)
+    assert abs(m.g - float(g["g"])) < 1e-15
+    # arma::expmat (Pade) vs symmetric eigendecomposition: same matrix to rounding
+    for nm in ("expK", "invexpK", "expK_half", "invexpK_half"):
+        assert rel(getattr(m, nm), g[nm]) < 1e-12
+    # from here on use the reference's matrices bit-for-bit
+    m.expK, m.invexpK, m.expK_half, m.invexpK_half = g["expK"], g["invexpK"], g["expK_half"], g["invexpK_half"]
+    for i in range(d.n_stack):
+        assert rel(d.calculate_Bbar(i), g["Bbar0"][i]) < TOL
+    d.init_stacks()
+    d.init_greenfunctions()
+    for i in range(d.n_stack):
+        assert rel(d.stack[i].to_matrix(), g["stack0_prod"][i]) < 1e-9
+        assert np.allclose(np.sort(d.stack[i].d), np.sort(g["stack0_d"][i]), rtol=1e-8)
+    assert rel(d.G, g["G0"]) < TOL
+    assert abs(d.log_det_M - float(g["logdet0"])) < TOL * abs(float(g["logdet0"]))
+    assert abs(m.global_action(d.log_det_M) - float(g["action0"])) < TOL * abs(float(g["action0"]))
+    den, docc, sw, corr = O.observables(d.G)
+    assert np.allclose([den, docc, sw], g["obs0"], rtol=1e-10, atol=1e-12)
+    assert rel(corr, g["corr0"]) < TOL
+    assert rel(d.half_wrap(), g["half_wrap0"]) < TOL
+
+
+@pytest.mark.parametrize("name", ["c0", "r7", "c1s"])
+def test_one_slice_step_by_step(name):
+    """Teacher-forced: wrap of G(0), then every proposal of slice 0 (R, Delta, decision), then wrap back."""
+    g = load(f"traj_{name}.npz")
+    m, d, seed, _ = build_from_gold(g)
+    m.expK, m.invexpK = g["expK"], g["invexpK"]
+    G = d.wrap_forward(g["G0"], 0)
+    assert rel(G, g["G_wrap_fwd0"]) < TOL
+    G = g["G_wrap_fwd0"].copy()
+    perm, k, u = O.rng_tape(O.MT19937(seed), m.ns, 1)
+    assert np.array_equal(perm[0], g["tape_perm"][0]) and np.array_equal(k[0], g["tape_k"][0])
+    assert np.array_equal(u[0], g["tape_u"][0])
+    d.trace = []
+    d.local_update(G, 0, perm[0], k[0], u[0])
+    R = np.array([t[3] for t in d.trace])
+    dl = np.array([t[4] for t in d.trace])
+    acc = np.array([t[6] for t in d.trace])
+    assert np.array_equal(acc, g["slice0_accept"])
+    assert np.allclose(R, g["slice0_R"], rtol=1e-11) and np.allclose(dl, g["slice0_delta"], rtol=1e-12)
+    assert np.array_equal(m.fields[0], g["slice0_fields"])
+    assert rel(G, g["slice0_G"]) < TOL
+    assert rel(d.wrap_backward(g["slice0_G"], 0), g["slice0_G_wrap_bwd"]) < TOL
+
+
+@pytest.mark.parametrize("name", ["c0", "r7", "c1s"])
+def test_trajectory(name):
+    """Free-running sweeps on the reference's RNG stream: identical fields after every half sweep."""
+    g = load(f"traj_{name}.npz")
+    m, d, seed, n_sweeps = build_from_gold(g)
+    m.expK, m.invexpK = g["expK"], g["invexpK"]
+    nt = m.nt
+    gen = O.MT19937(seed)
+    perm, k, u = O.rng_tape(gen, m.ns, 2 * nt * n_sweeps)
+    assert np.array_equal(perm, g["tape_perm"]) and np.array_equal(k, g["tape_k"]) and np.array_equal(u, g["tape_u"])
+    d.init_stacks()
+    d.init_greenfunctions()
+    for s in range(n_sweeps):
+        o = 2 * nt * s
+        d.sweep_0_to_beta((perm[o:o + nt], k[o:o + nt], u[o:o + nt]))
+        assert np.array_equal(m.fields, g["traj_fields"][2 * s])
+        assert rel(d.G, g["traj_G"][2 * s]) < 1e-9
+        assert abs(d.log_det_M - g["traj_logdet"][2 * s]) < 1e-9 * abs(g["traj_logdet"][2 * s])
+        d.sweep_beta_to_0((perm[o + nt:o + 2 * nt], k[o + nt:o + 2 * nt], u[o + nt:o + 2 * nt]))
+        assert np.array_equal(m.fields, g["traj_fields"][2 * s + 1])
+        assert rel(d.G, g["traj_G"][2 * s + 1]) < 1e-9
+    assert abs(d.acc_rate - float(g["traj_acc_rate"])) < 1e-12
+    # check_error values are differences of O(1) numbers at the 1e-7..1e-11 level: same envelope only
+    assert d.max_err < 10 * float(g["traj_max_err"]) + 1e-9
+    assert abs(m.global_action(d.log_det_M) - float(g["traj_action"])) < 1e-9 * abs(float(g["traj_action"]))
+    den, docc, sw, corr = O.observables(d.G)
+    assert np.allclose([den, docc, sw], g["traj_obs"], rtol=1e-9)
+    assert rel(corr, g["traj_corr"]) < 1e-9
+    for i in range(d.n_stack):
+        assert rel(d.stack[i].to_matrix(), g["traj_stack_prod"][i]) < 1e-8
+
+
+@pytest.mark.parametrize("n", [12, 36])
+def test_stablelinalg_golden(n):
+    g = load("stablelinalg.npz")
+    p = f"n{n}_"
+    M1, M2 = g[p + "M1"], g[p + "M2"]
+    F1, F2 = O.to_LDR(M1), O.to_LDR(M2)
+    for F, nm, M in ((F1, "F1", M1), (F2, "F2", M2)):
+        assert rel(F.to_matrix(), M) < 1e-12
+        assert np.allclose(F.d, g[p + nm + "_d"], rtol=1e-10)        # same pivoting => same |diag R|
+        assert rel(np.abs(F.L), np.abs(g[p + nm + "_L"])) < 1e-8      # columns up to sign
+        assert np.allclose(F.L.T @ F.L, np.eye(n), atol=1e-13)
+    G1 = O.LDR(g[p + "F1_L"], g[p + "F1_d"], g[p + "F1_R"])
+    G2 = O.LDR(g[p + "F2_L"], g[p + "F2_d"], g[p + "F2_R"])
+    for nm, F in (("mat_mul_ldr", O.mat_mul_ldr(M2, G1)), ("ldr_mul_mat", O.ldr_mul_mat(G1, M2)), ("ldr_mul_ldr", O.ldr_mul_ldr(G1, G2))):
+        want = (g[p + nm + "_L"] * g[p + nm + "_d"]) @ g[p + nm + "_R"]
+        assert rel(F.to_matrix(), want) < 1e-10
+        assert np.allclose(np.sort(F.d), np.sort(g[p + nm + "_d"]), rtol=1e-8)
+    G, ld = O.inv_I_plus_ldr(G1)
+    assert rel(G, g[p + "inv1_G"]) < TOL and abs(ld - float(g[p + "inv1_logdet"])) < TOL * max(1, abs(ld))
+    assert rel(O.inv_I_plus_ldr_mul_ldr(G1, G2), g[p + "inv2_G"]) < TOL
+    assert rel(O.inv_invldr_plus_ldr(G1, G2), g[p + "inv3_G"]) < TOL
+    # invariants 2 and 3 of SURVEY.md section 4 on a well-conditioned input
+    Mw = np.eye(n) * 0.5 + 0.05 * M1 / np.max(np.abs(M1))
+    Gw, ldw = O.inv_I_plus_ldr(O.to_LDR(Mw))
+    assert rel(Gw, np.linalg.inv(np.eye(n) + Mw)) < 1e-12
+    assert abs(ldw - np.linalg.slogdet(np.eye(n) + Mw)[1]) < 1e-12
+
+
+def test_replica_exchange_golden():
+    """update::replica_exchange (source/update.cpp:47-117) on a 4-replica beta ladder, 2 attempts."""
+    g = load("exchange.npz")
+    L1, L2, U, t, mu, nt, n_stab = g["cfg"]
+    L1, L2, nt, n_stab = int(L1), int(L2), int(nt), int(n_stab)
+    sims = []
+    for r, beta in enumerate(g["betas"]):
+        m = O.Model(L1, L2, U, t, mu, float(beta), nt, fields=g["fields_before"][r].astype(np.int64))
+        d = O.DQMC(m, n_stab)
+        d.init_stacks()
+        d.init_greenfunctions()
+        sims.append(d)
+    for r, d in enumerate(sims):
+        assert abs(d.m.global_action(d.log_det_M) - g["action_before"][r]) < 1e-9 * abs(g["action_before"][r])
+    for a in range(2):
+        u = {r: float(g[f"u_next_{a}"][r]) for r in range(4)}
+        O.replica_exchange(sims, a + 1, u)
+        for r, d in enumerate(sims):
+            assert np.array_equal(d.m.fields, g[f"fields_after_{a}"][r]), f"attempt {a} rank {r}"
+            assert abs(d.log_det_M - g[f"logdet_after_{a}"][r]) < 1e-9 * abs(g[f"logdet_after_{a}"][r])
+            assert rel(d.G, g[f"G_after_{a}"][r]) < 1e-9
+
+
+def test_physics_invariants():
+    """SURVEY.md section 4, invariants 4-6 and 8 (no reference needed)."""
+    # U = 0: G = [I + exp(-beta K)]^-1, mu = 0 => density 1
+    m = O.Model(4, 4, 0.0, 1.0, 0.0, 2.0, 10, fields=O.random_fields(3, 10, 16))
+    d = O.DQMC(m, 5)
+    d.init_stacks(); d.init_greenfunctions()
+    K = O.build_K(4, 4, 1.0, 0.0)
+    assert rel(d.G, np.linalg.inv(np.eye(16) + O.expm_sym(-2.0 * K))) < 1e-11
+    assert abs(O.observables(d.G)[0] - 1.0) < 1e-12
+    # flip ratio and Sherman-Morrison vs brute force
+    m = O.Model(4, 4, 4.0, 1.0, -0.1, 2.0, 10, fields=O.random_fields(5, 10, 16))
+    d = O.DQMC(m, 5)
+    d.init_stacks(); d.init_greenfunctions()
+    G = d.wrap_forward(d.G, 0)  # Gtt[1]: B_0 leftmost, slice-0 updates act here
+    ld0, S0 = d.log_det_M, m.global_action(d.log_det_M)
+    i, new = 7, int(O.PROPOSAL[m.fields[0, 7], 1])
+    R, delta = m.local_update_ratio(G, 0, i, new)
+    G2 = G.copy()
+    O.Model.update_greens_local(G2, delta, i)
+    old = int(m.fields[0, i])
+    m.fields[0, i] = new
+    d2 = O.DQMC(m, 5)
+    d2.init_stacks(); d2.init_greenfunctions()
+    det_ratio = math.exp(2.0 * (d2.log_det_M - ld0))
+    boson, _ = m.bosonic_ratio(new, old)
+    assert abs(R / (O.GAMMA[new] / O.GAMMA[old] * boson) - det_ratio) < 1e-9 * det_ratio
+    assert rel(G2, d2.wrap_forward(d2.G, 0)) < 1e-9
+    assert abs((m.global_action(d2.log_det_M) - S0) + math.log(abs(R))) < 1e-9
+
+
+def _ref_or_skip():
+    from oracle import ref
+
+    if not ref.available():
+        pytest.skip("oracle/_ref not built (needs /root/reference at build time)")
+    return ref
+
+
+@pytest.mark.parametrize("cfg", [(6, 6, 4.0, 1.0, -0.1, 4.0, 40, 10, 31), (5, 3, 6.0, 1.0, 0.3, 2.0, 11, 4, 32)])
+def test_live_reference_trajectory(cfg):
+    """Fresh seeds against the live reference build: identical fields after a full sweep."""
+    ref = _ref_or_skip()
+    L1, L2, U, t, mu, beta, nt, n_stab, seed = cfg
+    s = ref.RefSim(L1, L2, U, t, mu, beta, nt, n_stab, seed)
+    m = O.Model(L1, L2, U, t, mu, beta, nt, fields=O.random_fields(seed, nt, L1 * L2))
+    assert np.array_equal(m.fields, s.fields())
+    m.expK, m.invexpK = s.expK(), s.invexpK()
+    d = O.DQMC(m, n_stab)
+    d.init_stacks(); d.init_greenfunctions()
+    assert rel(d.G, s.G(0)) < TOL
+    perm, k, u = O.rng_tape(O.MT19937(seed), m.ns, 2 * nt)
+    rp, rk, ru = s.rng_tape(2 * nt)
+    assert np.array_equal(perm, rp) and np.array_equal(k, rk) and np.array_equal(u, ru)
+    fd = os.open(os.devnull, os.O_WRONLY); saved = os.dup(2); os.dup2(fd, 2)
+    try:
+        s.sweep_fwd(); s.sweep_bwd()
+    finally:
+        os.dup2(saved, 2); os.close(fd); os.close(saved)
+    d.sweep_0_to_beta((perm[:nt], k[:nt], u[:nt]))
+    d.sweep_beta_to_0((perm[nt:], k[nt:], u[nt:]))
+    assert np.array_equal(m.fields, s.fields())
+    assert rel(d.G, s.G(0)) < 1e-9
+    assert abs(d.acc_rate - s.acc_rate()) < 1e-12
+
+
+def test_live_reference_stablelinalg():
+    ref = _ref_or_skip()
+    rng = np.random.default_rng(8)
+    n = 20
+    Q1, _ = np.linalg.qr(rng.standard_normal((n, n)))
+    Q2, _ = np.linalg.qr(rng.standard_normal((n, n)))
+    M = (Q1 * np.exp(np.linspace(7, -7, n))) @ Q2
+    Lr, dr, Rr = ref.to_LDR(M)
+    F = O.to_LDR(M)
+    assert np.allclose(F.d, dr, rtol=1e-10) and rel(np.abs(F.L), np.abs(Lr)) < 1e-8
+    Gr, ldr = ref.inv_I_plus_ldr((Lr, dr, Rr))
+    Go, ldo = O.inv_I_plus_ldr(O.LDR(Lr, dr, Rr))
+    assert rel(Go, Gr) < TOL and abs(ldo - ldr) < 1e-10 * max(1, abs(ldr))

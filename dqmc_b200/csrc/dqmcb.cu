@@ -553,6 +553,14 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
     CKC(cudaFuncSetAttribute(k_init_green, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
     CKC(cudaFuncSetAttribute(k_ldr_op, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
     { const char* fg = getenv("DQMCB_FORCE_GENERIC"); ctx->force_generic = fg && fg[0] == (char)49; }
+    {
+        const char* pp = getenv("DQMCB_PHASE_PROF");
+        if (pp && pp[0] == (char)49) {
+            CKC(cudaMalloc(&p.prof, 64 * sizeof(long long)));
+            CKC(cudaMemset(p.prof, 0, 64 * sizeof(long long)));
+            CKC(cudaMemcpyToSymbol(dq::g_dq_prof, &p.prof, sizeof(p.prof)));
+        }
+    }
     CKC(fast64_setup(ctx));
 #undef CKC
     *out = ctx;
@@ -586,6 +594,17 @@ void dqmcb_destroy(dqmcb_ctx* ctx) {
     cudaFree(ctx->d_tape_k);
     cudaFree(ctx->d_tape_u);
     cudaFree(ctx->d_mt);
+    if (p.prof) {
+        long long h[64];
+        cudaDeviceSynchronize();
+        if (cudaMemcpy(h, p.prof, sizeof(h), cudaMemcpyDeviceToHost) == cudaSuccess) {
+            fprintf(stderr, "[dqmcb phase prof] clock64 offsets from stamp 0, last instrumented launch (CTA 0):");
+            for (int i = 1; i < 64; ++i)
+                if (h[i]) fprintf(stderr, " %d:%lld", i, h[i] - h[0]);
+            fprintf(stderr, "\n");
+        }
+        cudaFree(p.prof);
+    }
     drain_spans(ctx);
     delete ctx;
 }

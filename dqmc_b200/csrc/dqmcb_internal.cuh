@@ -50,7 +50,14 @@ struct Params {
     double lut_ev[4];      // exp(+g eta)                         source/model.cpp:69
     double lut_iev[4];     // exp(-g eta)                         source/model.cpp:81
     double lut_action[4];  // alpha g eta(s) + log gamma(s)       source/model.cpp:153-154
+    long long* prof;       // development aid (DQMCB_PHASE_PROF=1): clock64 stamps of CTA 0, else null
 };
+
+// phase stamp k of CTA 0 / thread 0 (no-op unless the context was created with DQMCB_PHASE_PROF=1)
+#define DQ_PH(p, k)                                                                         \
+    do {                                                                                    \
+        if ((p).prof && blockIdx.x == 0 && threadIdx.x == 0) (p).prof[k] = clock64();       \
+    } while (0)
 
 }  // namespace dq
 

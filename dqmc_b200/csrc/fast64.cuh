@@ -72,10 +72,12 @@ __device__ inline void tile_fetch(FWork<N>& wk, double* dst, const double* __res
 
 // to_LDR on tile A (destroyed): Q -> tile Qo, D^-1 R P^T -> tile Ro, |diag R| -> dout
 template <int N>
-__device__ void f_to_ldr(FWork<N>& wk, double* A, double* Qo, double* Ro, double* dout) {
+__device__ void f_to_ldr(const Params& p, FWork<N>& wk, double* A, double* Qo, double* Ro, double* dout) {
     constexpr int LDT = Tile<N>::LDT;
     __syncthreads();
-    qrp_tile<N>(A, wk.tau, wk.jpvt, wk.vn1, wk.vn2);
+    DQ_PH(p, 20);
+    qrp_tile<N>(A, wk.tau, wk.jpvt, wk.vn1, wk.vn2, wk.prow);
+    DQ_PH(p, 21);
     for (int j = threadIdx.x; j < N; j += blockDim.x) {
         const double dj = fabs(A[j + (size_t)j * LDT]);
         dout[j] = dj;
@@ -87,8 +89,10 @@ __device__ void f_to_ldr(FWork<N>& wk, double* A, double* Qo, double* Ro, double
         const double v = (i <= j) ? wk.vn1[i] * A[i + (size_t)j * LDT] : 0.0;
         Ro[i + (size_t)wk.jpvt[j] * LDT] = v;
     }
+    DQ_PH(p, 22);
     form_q_tile<N>(Qo, A, wk.tau);
     __syncthreads();
+    DQ_PH(p, 23);
 }
 
 template <int N>
@@ -116,23 +120,23 @@ __device__ double f_inv_I_plus_ldr(const Params& p, FWork<N>& wk, const double* 
     double part = 0.0;
     for (int i = threadIdx.x; i < N; i += blockDim.x) part += (d[i] >= 1.0) ? log(d[i]) : 0.0;
     const double logdl = cta_reduce_sum(part, wk.red);  // contains barriers
-    lu_tile<N>(t1, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    lu_tile<N>(t1, wk.ipiv, reinterpret_cast<int*>(wk.jrow), wk.prow, wk.info);
     f_note_fail<N>(p, wk, 10);
     f_set_diag<N>(t2, wk.sv[0]);
     __syncthreads();
-    lu_solve_tile<N>(t1, wk.ipiv, t2, 1, LDT);  // X
+    lu_solve_tile<N>(t1, reinterpret_cast<int*>(wk.jrow), wk.prow, t2, 1, LDT);  // X
     __syncthreads();
     for (int e = threadIdx.x; e < N * N; e += blockDim.x) {  // t0 <- M^T,  M = X + L D_small
         const int r = e % N, c = e / N;
         t0[c + (size_t)r * LDT] = t2[r + (size_t)c * LDT] + L[r + (size_t)c * N] * wk.sv[1][c];
     }
     __syncthreads();
-    lu_tile<N>(t0, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    lu_tile<N>(t0, wk.ipiv, reinterpret_cast<int*>(wk.jrow), wk.prow, wk.info);
     f_note_fail<N>(p, wk, 11);
     part = 0.0;
     for (int i = threadIdx.x; i < N; i += blockDim.x) part += log(fabs(t0[i + (size_t)i * LDT]));
     const double logm = cta_reduce_sum(part, wk.red);
-    lu_solve_tile<N>(t0, wk.ipiv, t2, LDT, 1);  // M^T Gt = X^T, in place on X viewed transposed
+    lu_solve_tile<N>(t0, reinterpret_cast<int*>(wk.jrow), wk.prow, t2, LDT, 1);  // M^T Gt = X^T, in place on X viewed transposed
     __syncthreads();
     return logdl + logm;
 }
@@ -149,29 +153,37 @@ __device__ void f_inv_I_plus_ldr_mul_ldr(const Params& p, FWork<N>& wk, const do
     split_d(d2, N, wk.sv[2], wk.sv[3]);
     tile_load_global<N>(t0, R2);
     __syncthreads();
-    lu_tile<N>(t0, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    DQ_PH(p, 5);
+    lu_tile<N>(t0, wk.ipiv, reinterpret_cast<int*>(wk.jrow), wk.prow, wk.info);
+    DQ_PH(p, 6);
     f_note_fail<N>(p, wk, 12);
     f_set_diag<N>(t1, wk.sv[2]);
     __syncthreads();
-    lu_solve_tile<N>(t0, wk.ipiv, t1, 1, LDT);  // X = R2^-1 D2l^-1  (t1)
+    lu_solve_tile<N>(t0, reinterpret_cast<int*>(wk.jrow), wk.prow, t1, 1, LDT);  // X = R2^-1 D2l^-1  (t1)
     __syncthreads();
+    DQ_PH(p, 7);
     // M = D1l^-1 (L1^T X) + D1s (R1 (L2 D2s))   (t2).  The column scaling by D2s is applied to the
     // product instead of to L2 first: identical in exact arithmetic, no cancellation involved.
     cta_mma<N, false>(t2, LDT, L1, N, 1, t1, 1, LDT, wk.sv[0], nullptr);
     __syncthreads();
     cta_mma<N, true>(t2, LDT, R1, 1, N, L2, 1, N, wk.sv[1], wk.sv[3]);
+    DQ_PH(p, 8);
     // RHS = D1l^-1 L1^T  (t0; the LU of R2 is dead)
     for (int e = threadIdx.x; e < N * N; e += blockDim.x) {
         const int c = e % N, r = e / N;
         t0[r + (size_t)c * LDT] = wk.sv[0][r] * L1[c + (size_t)r * N];
     }
     __syncthreads();
-    lu_tile<N>(t2, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    DQ_PH(p, 9);
+    lu_tile<N>(t2, wk.ipiv, reinterpret_cast<int*>(wk.jrow), wk.prow, wk.info);
+    DQ_PH(p, 10);
     f_note_fail<N>(p, wk, 13);
-    lu_solve_tile<N>(t2, wk.ipiv, t0, 1, LDT);  // Y (t0)
+    lu_solve_tile<N>(t2, reinterpret_cast<int*>(wk.jrow), wk.prow, t0, 1, LDT);  // Y (t0)
     __syncthreads();
+    DQ_PH(p, 11);
     cta_mma<N, false>(t2, LDT, t1, 1, LDT, t0, 1, LDT, nullptr, nullptr);  // G = X Y
     __syncthreads();
+    DQ_PH(p, 12);
 }
 
 }  // namespace dq
@@ -235,12 +247,14 @@ __global__ void __launch_bounds__(kThreads, 2) kf_stabilize(Params p, int l, int
     FWork<N> wk;
     fcarve<N>(wk, smem);
     const int i = l / p.n_stab;
+    DQ_PH(p, 0);
     f_bbar<N>(p, wk, w, i);  // -> t[0]
     double *t0 = wk.t[0], *t1 = wk.t[1], *t2 = wk.t[2];
     __syncthreads();
+    DQ_PH(p, 1);
     const bool first = (dir > 0) ? (i == 0) : (i == p.n_stack - 1);
     if (first) {
-        f_to_ldr<N>(wk, t0, t1, t2, wk.dnew);
+        f_to_ldr<N>(p, wk, t0, t1, t2, wk.dnew);
         tile_store_global<N>(fstkL(p, w, i), t1);
         tile_store_global<N>(fstkR(p, w, i), t2);
     } else if (dir > 0) {
@@ -249,7 +263,7 @@ __global__ void __launch_bounds__(kThreads, 2) kf_stabilize(Params p, int l, int
         tile_fetch<N>(wk, t1, fstkL(p, w, i - 1));
         __syncthreads();
         cta_mma<N, false>(t2, LDT, t0, 1, LDT, t1, 1, LDT, nullptr, wk.sv[0]);
-        f_to_ldr<N>(wk, t2, t0, t1, wk.dnew);
+        f_to_ldr<N>(p, wk, t2, t0, t1, wk.dnew);
         tile_store_global<N>(fstkL(p, w, i), t0);
         tile_fetch<N>(wk, t2, fstkR(p, w, i - 1));
         __syncthreads();
@@ -260,7 +274,7 @@ __global__ void __launch_bounds__(kThreads, 2) kf_stabilize(Params p, int l, int
         tile_fetch<N>(wk, t1, fstkR(p, w, i + 1));
         __syncthreads();
         cta_mma<N, false>(t2, LDT, t1, 1, LDT, t0, 1, LDT, wk.sv[0], nullptr);
-        f_to_ldr<N>(wk, t2, t0, t1, wk.dnew);
+        f_to_ldr<N>(p, wk, t2, t0, t1, wk.dnew);
         tile_store_global<N>(fstkR(p, w, i), t1);
         tile_fetch<N>(wk, t2, fstkL(p, w, i + 1));
         __syncthreads();
@@ -268,6 +282,7 @@ __global__ void __launch_bounds__(kThreads, 2) kf_stabilize(Params p, int l, int
     }
     fstore_d(fstkD(p, w, i), wk.dnew, N);
     __syncthreads();
+    DQ_PH(p, 4);
     const bool at_end = (dir > 0) ? (l == p.nt - 1) : (l == 0);
     if (at_end) {
         const double ld_ = f_inv_I_plus_ldr<N>(p, wk, fstkL(p, w, i), fstkD(p, w, i), fstkR(p, w, i));
@@ -282,13 +297,23 @@ __global__ void __launch_bounds__(kThreads, 2) kf_stabilize(Params p, int l, int
     // check_error + install
     double* Gg = p.G + (size_t)w * N * N;
     double emax = 0.0;
-    for (int e = threadIdx.x; e < N * N; e += blockDim.x) {
-        const int r = e % N, c = e / N;
-        const double v = t2[r + (size_t)c * LDT];
-        emax = fmax(emax, fabs(Gg[e] - v));
-        Gg[e] = v;
+    {
+        constexpr int PER = N * N / 2 / kThreads;  // double2 elements per thread, all loads issued up front
+        static_assert((N * N / 2) % kThreads == 0, "check_error tiling");
+        double2 old[PER];
+#pragma unroll
+        for (int u = 0; u < PER; ++u) old[u] = reinterpret_cast<const double2*>(Gg)[threadIdx.x + u * kThreads];
+#pragma unroll
+        for (int u = 0; u < PER; ++u) {
+            const int e2 = threadIdx.x + u * kThreads;
+            const int r = (e2 % (N / 2)) * 2, c = e2 / (N / 2);
+            const double2 v = *reinterpret_cast<const double2*>(t2 + r + (size_t)c * LDT);
+            emax = fmax(emax, fmax(fabs(old[u].x - v.x), fabs(old[u].y - v.y)));
+            reinterpret_cast<double2*>(Gg)[e2] = v;
+        }
     }
     emax = cta_reduce_max(emax, wk.red);
+    DQ_PH(p, 13);
     if (threadIdx.x == 0) {
         p.err_max[w] = fmax(p.err_max[w], emax);
         p.err_sum[w] += emax;
@@ -308,7 +333,7 @@ __global__ void __launch_bounds__(kThreads, 2) kf_init_stacks(Params p) {
     for (int i = p.n_stack - 1; i >= 0; --i) {
         f_bbar<N>(p, wk, w, i);
         __syncthreads();
-        f_to_ldr<N>(wk, t0, t1, t2, wk.sv[2]);  // Bbar_ldr: L2 = t1, R2 = t2, d2 = sv[2]
+        f_to_ldr<N>(p, wk, t0, t1, t2, wk.sv[2]);  // Bbar_ldr: L2 = t1, R2 = t2, d2 = sv[2]
         if (i == p.n_stack - 1) {
             tile_store_global<N>(fstkL(p, w, i), t1);
             tile_store_global<N>(fstkR(p, w, i), t2);
@@ -320,7 +345,7 @@ __global__ void __launch_bounds__(kThreads, 2) kf_init_stacks(Params p) {
             cta_mma<N, false>(t0, LDT, fstkR(p, w, i + 1), 1, N, t1, 1, LDT, wk.sv[0], wk.sv[2]);
             // park R2 in the (not yet written) global R slot of entry i while the tiles are busy
             tile_store_global<N>(fstkR(p, w, i), t2);
-            f_to_ldr<N>(wk, t0, t1, t2, wk.dnew);  // Q = t1, R_new = t2
+            f_to_ldr<N>(p, wk, t0, t1, t2, wk.dnew);  // Q = t1, R_new = t2
             cta_mma<N, false>(fstkL(p, w, i), N, fstkL(p, w, i + 1), 1, N, t1, 1, LDT, nullptr, nullptr);
             tile_load_global<N>(t0, fstkR(p, w, i));  // R2 back (same CTA wrote it: generic proxy)
             __syncthreads();

@@ -13,6 +13,13 @@
 
 namespace dq {
 
+// development aid: set through DQMCB_PHASE_PROF=1 (see dqmcb.cu); stamps from inside the tile routines
+__device__ long long* g_dq_prof = nullptr;
+#define DQ_PHG(k)                                                                    \
+    do {                                                                             \
+        if (g_dq_prof && blockIdx.x == 0 && (threadIdx.x & 31) == 0) g_dq_prof[k] = clock64(); \
+    } while (0)
+
 template <int N>
 struct Tile {
     static constexpr int LDT = N + 4;
@@ -210,16 +217,22 @@ __device__ __forceinline__ void tile_load_global(double* __restrict__ tile, cons
 }
 
 // ------------------------------------------------------------------------------------------------
-// Column-pivoted Householder QR (dlaqp2 semantics, see linalg.cuh::cta_qrp) for compile-time N <= 64,
-// N multiple of 32 not required; each lane owns rows lane and lane+32 of a column.
+// Column-pivoted Householder QR (dlaqp2 semantics, see linalg.cuh::cta_qrp) for compile-time N <= 64;
+// each lane owns rows lane and lane+32 of a column.
+//
+// Two block barriers per column.  Warp 0 runs the serial part (partial-norm down-date of the previous
+// step for all columns at once, pivot choice, column swap, dlarfg); then all warps apply the
+// reflector to the trailing columns, each warp taking up to eight columns in two passes of four so
+// that four shuffle reductions are in flight together.  The new row-j element of every column is
+// parked in `arow` for the deferred down-date (same arithmetic as dlaqp2, executed one step later).
 // ------------------------------------------------------------------------------------------------
 template <int N>
 __device__ void qrp_tile(double* __restrict__ A, double* __restrict__ tau, int* __restrict__ jpvt, double* __restrict__ vn1,
-                         double* __restrict__ vn2) {
+                         double* __restrict__ vn2, double* __restrict__ arow) {
     static_assert(N <= 64, "qrp_tile holds two rows per lane");
     constexpr int LDT = Tile<N>::LDT;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    const double tol3z = 1.0536712127723509e-08;
+    const double tol3z = 1.0536712127723509e-08;  // sqrt(dlamch('Epsilon'))
     const int rA = lane, rB = lane + 32;
     const bool hasB = rB < N, hasA = rA < N;
     for (int c = warp; c < N; c += nwarps) {
@@ -236,6 +249,46 @@ __device__ void qrp_tile(double* __restrict__ A, double* __restrict__ tau, int* 
     for (int j = 0; j < N; ++j) {
         double* colj = A + (size_t)j * LDT;
         if (warp == 0) {
+            // ---- deferred down-date of step j-1 for the columns c >= j (lane: c = j + lane, j + lane + 32)
+            if (j > 0) {
+                unsigned need = 0;
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int cc = j + lane + 32 * h;
+                    int recompute = 0;
+                    if (cc < N) {
+                        const double v1 = vn1[cc];
+                        if (v1 != 0.0) {
+                            double temp = fabs(arow[cc]) / v1;
+                            temp = fmax(1.0 - temp * temp, 0.0);
+                            const double q = v1 / vn2[cc];
+                            if (temp * (q * q) <= tol3z)
+                                recompute = 1;
+                            else
+                                vn1[cc] = v1 * sqrt(temp);
+                        }
+                    }
+                    const unsigned m = __ballot_sync(DQ_FULL, recompute);
+                    need |= m ? (1u << h) : 0u;
+                    // rare: recompute the norm of rows >= j of the flagged columns, whole warp per column
+                    unsigned mm = m;
+                    while (mm) {
+                        const int b = __ffs(mm) - 1;
+                        mm &= mm - 1;
+                        const int cr = j + b + 32 * h;
+                        const double* cp = A + (size_t)cr * LDT;
+                        const double xs = (rA >= j && hasA) ? cp[rA] : 0.0, ys = (rB >= j && hasB) ? cp[rB] : 0.0;
+                        const double nr = sqrt(warp_sum(fma(xs, xs, ys * ys)));
+                        if (lane == 0) {
+                            vn1[cr] = nr;
+                            vn2[cr] = nr;
+                        }
+                    }
+                }
+                (void)need;
+                __syncwarp();
+            }
+            // ---- pivot: first column of maximal partial norm among j..N-1 (idamax semantics)
             double best = -1.0;
             int bi = j;
             {
@@ -277,13 +330,13 @@ __device__ void qrp_tile(double* __restrict__ A, double* __restrict__ tau, int* 
                     vn2[bi] = vn2[j];
                 }
             }
-            // dlarfg on rows j.. of the pivot column (held in x, y)
+            // ---- dlarfg on rows j.. of the pivot column (held in x, y)
             const double alpha = __shfl_sync(DQ_FULL, (j < 32) ? x : y, j & 31);
             const double xs = (rA > j) ? x : 0.0, ys = (rB > j && hasB) ? y : 0.0;
             const double xnorm = sqrt(warp_sum(fma(xs, xs, ys * ys)));
             double t = 0.0;
             if (xnorm != 0.0) {
-                const double beta = -copysign(hypot(alpha, xnorm), alpha);
+                const double beta = -copysign(sqrt(fma(alpha, alpha, xnorm * xnorm)), alpha);
                 t = (beta - alpha) / beta;
                 const double scal = 1.0 / (alpha - beta);
                 if (rA > j) x *= scal;
@@ -298,72 +351,35 @@ __device__ void qrp_tile(double* __restrict__ A, double* __restrict__ tau, int* 
         __syncthreads();
         const double t = tau[j];
         const double vA = (rA > j && hasA) ? colj[rA] : 0.0, vB = (rB > j && hasB) ? colj[rB] : 0.0;
-        // two columns per pass for ILP on the shuffle reductions
-        for (int c = j + 1 + 2 * warp; c < N; c += 2 * nwarps) {
-            const bool two = c + 1 < N;
-            double* c0p = A + (size_t)c * LDT;
-            double* c1p = A + (size_t)(two ? c + 1 : c) * LDT;
-            double a0 = hasA ? c0p[rA] : 0.0, b0 = hasB ? c0p[rB] : 0.0;
-            double a1 = hasA ? c1p[rA] : 0.0, b1 = hasB ? c1p[rB] : 0.0;
-            double s0 = fma(vA, a0, vB * b0), s1 = fma(vA, a1, vB * b1);
+        for (int c0 = j + 1 + warp; c0 < N; c0 += 4 * nwarps) {
+            double a[4], b[4], s[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int c = c0 + q * nwarps;
+                const double* cp = A + (size_t)((c < N) ? c : c0) * LDT;
+                a[q] = hasA ? cp[rA] : 0.0;
+                b[q] = hasB ? cp[rB] : 0.0;
+                s[q] = fma(vA, a[q], vB * b[q]);
+            }
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) {
-                s0 += __shfl_xor_sync(DQ_FULL, s0, o);
-                s1 += __shfl_xor_sync(DQ_FULL, s1, o);
+#pragma unroll
+                for (int q = 0; q < 4; ++q) s[q] += __shfl_xor_sync(DQ_FULL, s[q], o);
             }
-            const double aj0 = __shfl_sync(DQ_FULL, (j < 32) ? a0 : b0, j & 31);
-            const double aj1 = __shfl_sync(DQ_FULL, (j < 32) ? a1 : b1, j & 31);
-            const double w0 = t * (aj0 + s0), w1 = t * (aj1 + s1);
-            a0 = fma(-w0, vA, a0);
-            b0 = fma(-w0, vB, b0);
-            a1 = fma(-w1, vA, a1);
-            b1 = fma(-w1, vB, b1);
-            const double an0 = aj0 - w0, an1 = aj1 - w1;
-            if (rA == j) {
-                a0 = an0;
-                a1 = an1;
-            }
-            if (rB == j) {
-                b0 = an0;
-                b1 = an1;
-            }
-            if (rA >= j && hasA) {
-                c0p[rA] = a0;
-                if (two) c1p[rA] = a1;
-            }
-            if (rB >= j && hasB) {
-                c0p[rB] = b0;
-                if (two) c1p[rB] = b1;
-            }
-            // partial-norm down-date: lane 0 -> column c, lane 1 -> column c+1
-            int recompute = 0;
-            if (lane < 2 && (lane == 0 || two)) {
-                const int cc = c + lane;
-                const double anew = lane ? an1 : an0;
-                const double v1 = vn1[cc];
-                if (v1 != 0.0) {
-                    double temp = fabs(anew) / v1;
-                    temp = fmax(1.0 - temp * temp, 0.0);
-                    const double q = v1 / vn2[cc];
-                    if (temp * (q * q) <= tol3z)
-                        recompute = 1;
-                    else
-                        vn1[cc] = v1 * sqrt(temp);
-                }
-            }
-            const unsigned rmask = __ballot_sync(DQ_FULL, recompute);
-            if (rmask) {
-                const double xs0 = (rA > j) ? a0 : 0.0, ys0 = (rB > j && hasB) ? b0 : 0.0;
-                const double xs1 = (rA > j) ? a1 : 0.0, ys1 = (rB > j && hasB) ? b1 : 0.0;
-                const double n0 = sqrt(warp_sum(fma(xs0, xs0, ys0 * ys0)));
-                const double n1 = sqrt(warp_sum(fma(xs1, xs1, ys1 * ys1)));
-                if (lane == 0 && (rmask & 1)) {
-                    vn1[c] = n0;
-                    vn2[c] = n0;
-                }
-                if (lane == 1 && (rmask & 2)) {
-                    vn1[c + 1] = n1;
-                    vn2[c + 1] = n1;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int c = c0 + q * nwarps;
+                const double aj = __shfl_sync(DQ_FULL, (j < 32) ? a[q] : b[q], j & 31);
+                const double w = t * (aj + s[q]);
+                const double an = aj - w;
+                double na = fma(-w, vA, a[q]), nb = fma(-w, vB, b[q]);
+                if (rA == j) na = an;
+                if (rB == j) nb = an;
+                if (c < N) {
+                    double* cp = A + (size_t)c * LDT;
+                    if (rA >= j && hasA) cp[rA] = na;
+                    if (rB >= j && hasB) cp[rB] = nb;
+                    if (lane == 0) arow[c] = an;
                 }
             }
         }
@@ -420,10 +436,18 @@ __device__ void form_q_tile(double* __restrict__ Q, const double* __restrict__ V
 }
 
 // ------------------------------------------------------------------------------------------------
-// LU with partial pivoting (dgetf2 semantics, see linalg.cuh::cta_lu), compile-time N <= 64.
+// LU with partial pivoting (dgetf2 semantics: arma::solve / arma::log_det -> dgetrf), N <= 64.
+//
+// Right-looking, ONE block barrier per column, with look-ahead: in step j warp 0 updates column j+1
+// first and immediately searches its pivot (from registers), while the other warps update the rest of
+// the trailing matrix; the last warp finalises column j-1 (multipliers) and applies the row
+// interchange to the columns left of j.  Every warp handles whole columns (lane = rows lane, lane+32),
+// so the row interchange of step j is folded into the column update and needs no staging vectors.
+// Outputs besides the in-place factors: ipiv (LAPACK style), perm (perm[i] = original row now at
+// position i, i.e. the accumulated interchanges), rdiag[j] = 1 / U(j,j).
 // ------------------------------------------------------------------------------------------------
 template <int N>
-__device__ void lu_tile(double* __restrict__ A, int* __restrict__ ipiv, double* __restrict__ prow, double* __restrict__ jrow,
+__device__ void lu_tile(double* __restrict__ A, int* __restrict__ ipiv, int* __restrict__ perm, double* __restrict__ rdiag,
                         int* __restrict__ info) {
     static_assert(N <= 64, "lu_tile holds two rows per lane");
     constexpr int LDT = Tile<N>::LDT;
@@ -431,133 +455,169 @@ __device__ void lu_tile(double* __restrict__ A, int* __restrict__ ipiv, double* 
     const int rA = lane, rB = lane + 32;
     const bool hasA = rA < N, hasB = rB < N;
     if (threadIdx.x == 0) *info = 0;
-    int prev_p = 0;
-    double prev_rinv = 0.0, prev_jrowj = 0.0;
-    for (int j = 0; j <= N; ++j) {
-        if (warp == 0) {
-            if (j > 0) {  // deferred scaling of column j-1 (rows >= j)
-                double* colq = A + (size_t)(j - 1) * LDT;
-                if (rA >= j && hasA) colq[rA] = ((rA == prev_p) ? prev_jrowj : colq[rA]) * prev_rinv;
-                if (rB >= j && hasB) colq[rB] = ((rB == prev_p) ? prev_jrowj : colq[rB]) * prev_rinv;
+    for (int i = threadIdx.x; i < N; i += blockDim.x) perm[i] = i;
+    if (warp == 0) {  // pivot of column 0
+        double best = hasA ? fabs(A[rA]) : -1.0;
+        int bi = rA;
+        if (hasB) {
+            const double v = fabs(A[rB]);
+            if (v > best) {
+                best = v;
+                bi = rB;
             }
-            if (j < N) {
-                const double* colj = A + (size_t)j * LDT;
-                double best = -1.0;
-                int bi = j;
-                if (rA >= j && hasA) {
-                    best = fabs(colj[rA]);
-                    bi = rA;
-                }
-                if (rB >= j && hasB) {
-                    const double v = fabs(colj[rB]);
-                    if (v > best) {
-                        best = v;
-                        bi = rB;
-                    }
-                }
+        }
 #pragma unroll
-                for (int o = 16; o > 0; o >>= 1) {
-                    const double ob = __shfl_xor_sync(DQ_FULL, best, o);
-                    const int oi = __shfl_xor_sync(DQ_FULL, bi, o);
-                    if (ob > best || (ob == best && oi < bi)) {
-                        best = ob;
-                        bi = oi;
-                    }
+        for (int o = 16; o > 0; o >>= 1) {
+            const double ob = __shfl_xor_sync(DQ_FULL, best, o);
+            const int oi = __shfl_xor_sync(DQ_FULL, bi, o);
+            if (ob > best || (ob == best && oi < bi)) {
+                best = ob;
+                bi = oi;
+            }
+        }
+        if (lane == 0) ipiv[0] = bi;
+    }
+    __syncthreads();
+    int prev_p = 0;
+    double prev_rinv = 0.0, prev_jj = 0.0, prev_piv = 0.0;
+    for (int j = 0; j < N; ++j) {
+        const int p = ipiv[j];
+        double* colj = A + (size_t)j * LDT;
+        const double piv = colj[p], jj = colj[j];
+        const double rinv = (piv != 0.0) ? 1.0 / piv : 0.0;
+        // multipliers of my rows after the interchange (row p now holds the old row j)
+        const double lA = (rA > j && hasA) ? ((rA == p) ? jj : colj[rA]) * rinv : 0.0;
+        const double lB = (rB > j && hasB) ? ((rB == p) ? jj : colj[rB]) * rinv : 0.0;
+        if (warp == nwarps - 1) {
+            if (j > 0) {  // finalise column j-1: U(j-1,j-1) and the multipliers below it
+                double* colq = A + (size_t)(j - 1) * LDT;
+                if (rA == j - 1) colq[rA] = prev_piv;
+                if (rB == j - 1) colq[rB] = prev_piv;
+                if (rA >= j && hasA) colq[rA] = ((rA == prev_p) ? prev_jj : colq[rA]) * prev_rinv;
+                if (rB >= j && hasB) colq[rB] = ((rB == prev_p) ? prev_jj : colq[rB]) * prev_rinv;
+                __syncwarp();
+            }
+            if (p != j) {  // interchange rows j and p in the columns left of j
+                for (int c = lane; c < j; c += 32) {
+                    double* cc = A + (size_t)c * LDT;
+                    const double t = cc[j];
+                    cc[j] = cc[p];
+                    cc[p] = t;
                 }
                 if (lane == 0) {
-                    ipiv[j] = bi;
-                    if (best == 0.0 && *info == 0) *info = j + 1;
+                    const int t = perm[j];
+                    perm[j] = perm[p];
+                    perm[p] = t;
                 }
             }
+            if (lane == 0) {
+                rdiag[j] = rinv;
+                if (piv == 0.0 && *info == 0) *info = j + 1;
+            }
         }
-        if (j == N) break;
-        __syncthreads();
-        const int p = ipiv[j];
-        for (int c = threadIdx.x; c < N; c += blockDim.x) {
-            prow[c] = A[p + (size_t)c * LDT];
-            jrow[c] = A[j + (size_t)c * LDT];
-        }
-        __syncthreads();
-        const double piv = prow[j];
-        const double rinv = (piv != 0.0) ? 1.0 / piv : 0.0;
-        const double jrowj = jrow[j];
-        for (int c = threadIdx.x; c < N; c += blockDim.x) {
-            A[j + (size_t)c * LDT] = prow[c];
-            if (p != j && c < j) A[p + (size_t)c * LDT] = jrow[c];
-        }
-        const double* colj = A + (size_t)j * LDT;
-        const double lA = (rA > j && hasA) ? ((rA == p) ? jrowj : colj[rA]) * rinv : 0.0;
-        const double lB = (rB > j && hasB) ? ((rB == p) ? jrowj : colj[rB]) * rinv : 0.0;
-        for (int c = j + 1 + warp; c < N; c += nwarps) {
-            double* colc = A + (size_t)c * LDT;
-            const double pc = prow[c], jc = jrow[c];
-            if (rA > j && hasA) colc[rA] = fma(-lA, pc, (rA == p) ? jc : colc[rA]);
-            if (rB > j && hasB) colc[rB] = fma(-lB, pc, (rB == p) ? jc : colc[rB]);
+        // trailing columns: index idx = c - (j+1) goes to warp idx % nwarps, four columns per pass
+        for (int c0 = j + 1 + warp; c0 < N; c0 += 4 * nwarps) {
+            double xa[4], xb[4], u[4], vj[4];
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int c = c0 + q * nwarps;
+                if (c < N) {
+                    const double* cc = A + (size_t)c * LDT;
+                    xa[q] = hasA ? cc[rA] : 0.0;
+                    xb[q] = hasB ? cc[rB] : 0.0;
+                    u[q] = cc[p];
+                    vj[q] = cc[j];
+                }
+            }
+            __syncwarp();  // every lane holds the old rows j and p before anyone overwrites them
+    #pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const int c = c0 + q * nwarps;
+                if (c < N) {
+                    double* cc = A + (size_t)c * LDT;
+                    const double na = fma(-lA, u[q], (rA == p) ? vj[q] : xa[q]);
+                    const double nb = fma(-lB, u[q], (rB == p) ? vj[q] : xb[q]);
+                    if (rA > j && hasA) cc[rA] = na;
+                    if (rB > j && hasB) cc[rB] = nb;
+                    if (rA == j) cc[rA] = u[q];
+                    if (rB == j) cc[rB] = u[q];
+                    if (c == j + 1) {  // look-ahead (warp 0, first pass): pivot of the next column
+                        double best = (rA > j && hasA) ? fabs(na) : -1.0;
+                        int bi = rA;
+                        if (rB > j && hasB) {
+                            const double v = fabs(nb);
+                            if (v > best) {
+                                best = v;
+                                bi = rB;
+                            }
+                        }
+#pragma unroll
+                        for (int o = 16; o > 0; o >>= 1) {
+                            const double ob = __shfl_xor_sync(DQ_FULL, best, o);
+                            const int oi = __shfl_xor_sync(DQ_FULL, bi, o);
+                            if (ob > best || (ob == best && oi < bi)) {
+                                best = ob;
+                                bi = oi;
+                            }
+                        }
+                        if (lane == 0) ipiv[j + 1] = bi;
+                                    }
+                }
+            }
         }
         prev_p = p;
         prev_rinv = rinv;
-        prev_jrowj = jrowj;
+        prev_jj = jj;
+        prev_piv = piv;
         __syncthreads();
     }
-    __syncthreads();
+    // column N-1 needs no finalisation: its pivot is the only remaining row
 }
 
 // dgetrs 'N' in place on an N x N right-hand side: element (i, c) at Bm[i*rsB + c*csB].
-// A team of 4 lanes owns one RHS column (rows i = 4 m + q in registers); requires blockDim = 4 N.
+// One thread per right-hand-side column with the whole column in registers (threads 0..N-1; the
+// triangular factors are read as warp-wide broadcasts, no shuffles, no barriers).  Uses perm / rdiag
+// from lu_tile.  Caller synchronises before and after.
 template <int N>
-__device__ void lu_solve_tile(const double* __restrict__ A, const int* __restrict__ ipiv, double* __restrict__ Bm, int rsB, int csB) {
-    static_assert(N % 4 == 0 && N <= 64, "lu_solve_tile layout");
+__device__ __noinline__ void lu_solve_tile(const double* __restrict__ A, const int* __restrict__ perm, const double* __restrict__ rdiag,
+                                           double* __restrict__ Bm, int rsB, int csB) {
+    static_assert(N % 2 == 0 && N <= 64, "lu_solve_tile layout");
     constexpr int LDT = Tile<N>::LDT;
-    constexpr int M = N / 4;
-    const int lane = threadIdx.x & 31;
-    const int q = threadIdx.x & 3, c = threadIdx.x >> 2;
-    if (c < N) {  // row interchanges, one thread per column does the (cheap, serial) dlaswp
-        if (q == 0) {
-            double* col = Bm + (size_t)c * csB;
-            for (int j = 0; j < N; ++j) {
-                const int p = ipiv[j];
-                if (p != j) {
-                    const double tmp = col[(size_t)j * rsB];
-                    col[(size_t)j * rsB] = col[(size_t)p * rsB];
-                    col[(size_t)p * rsB] = tmp;
-                }
-            }
-        }
-    }
-    __syncwarp();
-    const bool act = c < N;
-    double x[M];
+    const int c = threadIdx.x;
+    if (c >= N) return;
+    double x[N];
+    double* col = Bm + (size_t)c * csB;
 #pragma unroll
-    for (int m = 0; m < M; ++m) x[m] = act ? Bm[(size_t)(4 * m + q) * rsB + (size_t)c * csB] : 0.0;
-    const int team_base = lane & ~3;
-    // forward: L y = b (unit diagonal)
+    for (int i = 0; i < N; ++i) x[i] = col[(size_t)perm[i] * rsB];
+    // forward: L y = P b (unit diagonal); column k of L is contiguous
 #pragma unroll
     for (int k = 0; k < N - 1; ++k) {
-        const double xk = __shfl_sync(DQ_FULL, x[k >> 2], team_base | (k & 3));
+        const double xk = x[k];
         const double* lk = A + (size_t)k * LDT;
+        if ((k & 1) == 0) x[k + 1] = fma(-lk[k + 1], xk, x[k + 1]);
 #pragma unroll
-        for (int m = (k + 1) >> 2; m < M; ++m) {
-            const int i = 4 * m + q;
-            if (i > k) x[m] = fma(-lk[i], xk, x[m]);
+        for (int i = (k + 2) & ~1; i < N; i += 2) {
+            const double2 l2 = *reinterpret_cast<const double2*>(lk + i);
+            x[i] = fma(-l2.x, xk, x[i]);
+            x[i + 1] = fma(-l2.y, xk, x[i + 1]);
         }
     }
     // backward: U x = y
 #pragma unroll
     for (int k = N - 1; k >= 0; --k) {
+        const double xk = x[k] * rdiag[k];
+        x[k] = xk;
         const double* uk = A + (size_t)k * LDT;
-        double xk = __shfl_sync(DQ_FULL, x[k >> 2], team_base | (k & 3));
-        xk = xk / uk[k];
-        if ((k & 3) == q) x[k >> 2] = xk;
 #pragma unroll
-        for (int m = 0; m <= (k >> 2); ++m) {
-            const int i = 4 * m + q;
-            if (i < k) x[m] = fma(-uk[i], xk, x[m]);
+        for (int i = 0; i + 1 < k; i += 2) {
+            const double2 u2 = *reinterpret_cast<const double2*>(uk + i);
+            x[i] = fma(-u2.x, xk, x[i]);
+            x[i + 1] = fma(-u2.y, xk, x[i + 1]);
         }
+        if (k & 1) x[k - 1] = fma(-uk[k - 1], xk, x[k - 1]);
     }
-    if (act) {
 #pragma unroll
-        for (int m = 0; m < M; ++m) Bm[(size_t)(4 * m + q) * rsB + (size_t)c * csB] = x[m];
-    }
+    for (int i = 0; i < N; ++i) col[(size_t)i * rsB] = x[i];
 }
 
 }  // namespace dq

@@ -49,7 +49,8 @@ SYMBOLS = [
     "dqmcb_reset_stats", "dqmcb_device_ptr", "dqmcb_measure_equal_time", "dqmcb_global_action", "dqmcb_half_wrap",
     "dqmcb_run_sweeps_host", "dqmcb_to_LDR", "dqmcb_mat_mul_ldr", "dqmcb_ldr_mul_mat", "dqmcb_ldr_mul_ldr",
     "dqmcb_inv_I_plus_ldr", "dqmcb_inv_I_plus_ldr_mul_ldr", "dqmcb_partner_rank", "dqmcb_version",
-    "dqmcb_timing_enable", "dqmcb_timing_get",
+    "dqmcb_timing_enable", "dqmcb_timing_get", "dqmcb_inv_invldr_plus_ldr", "dqmcb_local_update_ratio",
+    "dqmcb_update_greens_local", "dqmcb_set_single_field",
 ]
 
 
@@ -77,6 +78,9 @@ def lib():
         L.dqmcb_destroy.argtypes = [C.c_void_p]
         L.dqmcb_rng_mode.argtypes = [C.c_void_p, C.c_int, C.c_uint64]
         L.dqmcb_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        L.dqmcb_update_greens_local.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int]
+        L.dqmcb_local_update_ratio.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, _dp, _dp]
+        L.dqmcb_set_single_field.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
         for name in ("dqmcb_synchronize", "dqmcb_init_stacks", "dqmcb_init_greenfunctions", "dqmcb_sweep_0_to_beta",
                      "dqmcb_sweep_beta_to_0", "dqmcb_reset_stats", "dqmcb_n_stack"):
             getattr(L, name).argtypes = [C.c_void_p]
@@ -266,6 +270,17 @@ class Context:
         self._ck(self.L.dqmcb_global_action(self.h, _d(S)))
         return S
 
+    def local_update_ratio(self, l, site, new_field):
+        R, dl = np.empty(self.W), np.empty(self.W)
+        self._ck(self.L.dqmcb_local_update_ratio(self.h, l, site, new_field, _d(R), _d(dl)))
+        return R, dl
+
+    def update_greens_local(self, walker, delta, site):
+        self._ck(self.L.dqmcb_update_greens_local(self.h, walker, C.c_double(delta), site))
+
+    def set_single_field(self, walker, l, site, value):
+        self._ck(self.L.dqmcb_set_single_field(self.h, walker, l, site, value))
+
     def half_wrap(self) -> np.ndarray:
         out = np.empty((self.W, self.N, self.N))
         self._ck(self.L.dqmcb_half_wrap(self.h, _d(out)))
@@ -345,6 +360,16 @@ def inv_I_plus_ldr_mul_ldr(F1, F2, device=0):
     G = np.empty((b, n, n))
     k = (_cm(L1), np.ascontiguousarray(d1), _cm(R1), _cm(L2), np.ascontiguousarray(d2), _cm(R2))
     _ckrc(lib().dqmcb_inv_I_plus_ldr_mul_ldr(device, n, b, *[_d(x) for x in k], _d(G)))
+    return _from_cm(G)
+
+
+def inv_invldr_plus_ldr(F1, F2, device=0):
+    L1, d1, R1 = _b(F1[0]), np.atleast_2d(np.asarray(F1[1], dtype=np.float64)), _b(F1[2])
+    L2, d2, R2 = _b(F2[0]), np.atleast_2d(np.asarray(F2[1], dtype=np.float64)), _b(F2[2])
+    b, n = L1.shape[0], L1.shape[1]
+    G = np.empty((b, n, n))
+    k = (_cm(L1), np.ascontiguousarray(d1), _cm(R1), _cm(L2), np.ascontiguousarray(d2), _cm(R2))
+    _ckrc(lib().dqmcb_inv_invldr_plus_ldr(device, n, b, *[_d(x) for x in k], _d(G)))
     return _from_cm(G)
 
 

@@ -350,10 +350,38 @@ __global__ void __launch_bounds__(kThreads) k_ldr_op(Params p, int op, LdrArgs a
         const double ld_ = dev_inv_I_plus_ldr(p, wk, n, L1, n, d1, R1, n);
         if (threadIdx.x == 0 && a.logdet) a.logdet[w] = ld_;
         cta_copy(G, n, b1, l1, n);
-    } else if (op == 5) {
-        dev_inv_I_plus_ldr_mul_ldr(p, wk, n, L1, d1, R1, L2, d2, R2, n);
+    } else if (op == 5 || op == 6) {
+        dev_inv_I_plus_ldr_mul_ldr(p, wk, n, L1, d1, R1, L2, d2, R2, n, op == 6);
         cta_copy(G, n, b2, l2, n);
     }
+}
+
+// AttractiveHubbard::local_update_ratio (source/model.cpp:109-122) for one proposal of every walker
+__global__ void k_ratio(Params p, int l, int site, int newf, double* out /*[W][2]*/) {
+    const int w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= p.W) return;
+    const int oldf = p.fields[((size_t)w * p.nt + l) * p.N + site];
+    const double gii = p.G[(size_t)w * p.N * p.N + site + (size_t)site * p.N];
+    const double delta = p.lut_delta[oldf * 4 + newf];
+    const double r = 1.0 + (1.0 - gii) * delta;
+    out[2 * w] = p.lut_gb[oldf * 4 + newf] * (r * r);
+    out[2 * w + 1] = delta;
+}
+
+// AttractiveHubbard::update_greens_local (source/model.cpp:124-138) on walker `w`: rank-1 Sherman-Morrison
+__global__ void __launch_bounds__(kThreads) k_rank1(Params p, int w, double delta, int site) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int n = p.N;
+    double* su = reinterpret_cast<double*>(smem);
+    double* sv = su + n;
+    double* G = p.G + (size_t)w * n * n;
+    const double pref = delta / (1.0 + (1.0 - G[site + (size_t)site * n]) * delta);
+    for (int t = threadIdx.x; t < n; t += blockDim.x) {
+        su[t] = __dmul_rn(pref, G[t + (size_t)site * n]);
+        sv[t] = G[site + (size_t)t * n] - ((t == site) ? 1.0 : 0.0);
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < n * n; e += blockDim.x) G[e] = __dadd_rn(G[e], __dmul_rn(su[e % n], sv[e / n]));
 }
 
 // =====================================================================================================
@@ -1145,6 +1173,53 @@ int dqmcb_inv_I_plus_ldr(int device, int n, int batch, const double* L, const do
 int dqmcb_inv_I_plus_ldr_mul_ldr(int device, int n, int batch, const double* L1, const double* d1, const double* R1, const double* L2,
                                  const double* d2, const double* R2, double* G) {
     return run_ldr_op(device, n, batch, 5, nullptr, L1, d1, R1, L2, d2, R2, nullptr, nullptr, nullptr, G, nullptr);
+}
+int dqmcb_inv_invldr_plus_ldr(int device, int n, int batch, const double* L1, const double* d1, const double* R1, const double* L2,
+                              const double* d2, const double* R2, double* G) {
+    return run_ldr_op(device, n, batch, 6, nullptr, L1, d1, R1, L2, d2, R2, nullptr, nullptr, nullptr, G, nullptr);
+}
+
+int dqmcb_local_update_ratio(dqmcb_ctx* ctx, int l, int site, int new_field, double* R, double* delta) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    if (int rc = check_l(ctx, l)) return rc;
+    if (site < 0 || site >= p.N || new_field < 0 || new_field > 3) {
+        ctx->err = "site or field value out of range";
+        return DQMCB_EINVAL;
+    }
+    k_ratio<<<(p.W + 127) / 128, 128, 0, ctx->stream>>>(p, l, site, new_field, ctx->d_scratchNN);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(ctx->stream));
+    std::vector<double> o((size_t)2 * p.W);
+    CK(cudaMemcpy(o.data(), ctx->d_scratchNN, o.size() * 8, cudaMemcpyDeviceToHost));
+    for (int w = 0; w < p.W; ++w) {
+        if (R) R[w] = o[2 * w];
+        if (delta) delta[w] = o[2 * w + 1];
+    }
+    return DQMCB_OK;
+}
+int dqmcb_update_greens_local(dqmcb_ctx* ctx, int walker, double delta, int site) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    if (walker < 0 || walker >= p.W || site < 0 || site >= p.N) {
+        ctx->err = "walker or site out of range";
+        return DQMCB_EINVAL;
+    }
+    k_rank1<<<1, kThreads, 2 * p.N * sizeof(double), ctx->stream>>>(p, walker, delta, site);
+    CK(cudaGetLastError());
+    return DQMCB_OK;
+}
+int dqmcb_set_single_field(dqmcb_ctx* ctx, int walker, int l, int site, int value) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    if (walker < 0 || walker >= p.W || l < 0 || l >= p.nt || site < 0 || site >= p.N || value < 0 || value > 3) {
+        ctx->err = "set_single_field: argument out of range";
+        return DQMCB_EINVAL;
+    }
+    const int8_t v = (int8_t)value;
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(p.fields + ((size_t)walker * p.nt + l) * p.N + site, &v, 1, cudaMemcpyHostToDevice));
+    return DQMCB_OK;
 }
 
 }  // extern "C"

@@ -168,7 +168,7 @@ __device__ double dev_inv_I_plus_ldr(const Params& p, Work& wk, int n, const dou
 // stablelinalg::inv_I_plus_ldr_mul_ldr (source/stablelinalg.cpp:128-158).  Result G in wk.b[2].
 // --------------------------------------------------------------------------------------------------
 __device__ void dev_inv_I_plus_ldr_mul_ldr(const Params& p, Work& wk, int n, const double* L1, const double* d1, const double* R1,
-                                           const double* L2, const double* d2, const double* R2, int ldg) {
+                                           const double* L2, const double* d2, const double* R2, int ldg, int rhs_mode = 0) {
     double* b0 = wk.b[0];
     double* b1 = wk.b[1];
     double* b2 = wk.b[2];
@@ -192,10 +192,11 @@ __device__ void dev_inv_I_plus_ldr_mul_ldr(const Params& p, Work& wk, int n, con
     // M = TermA + D1s (R1 (L2 D2s))
     cta_gemm<true>(b2, l2, R1, 1, ldg, b0, 1, l0, n, wk.sv[1], nullptr);
     __syncthreads();
-    // RHS = D1l^-1 L1^T  -> b0
+    // RHS = D1l^-1 L1^T  -> b0      (rhs_mode 1: RHS = D1s R1, stablelinalg::inv_invldr_plus_ldr,
+    //                                  source/stablelinalg.cpp:160-190 -- same M, different right-hand side)
     for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
         const int r = e % n, c = e / n;
-        b0[r + (size_t)c * l0] = wk.sv[0][r] * L1[c + (size_t)r * ldg];
+        b0[r + (size_t)c * l0] = rhs_mode ? wk.sv[1][r] * R1[r + (size_t)c * ldg] : wk.sv[0][r] * L1[c + (size_t)r * ldg];
     }
     __syncthreads();
     cta_lu(b2, l2, n, wk.ipiv, wk.prow, wk.jrow, wk.info);

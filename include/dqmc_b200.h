@@ -145,6 +145,18 @@ int dqmcb_inv_I_plus_ldr(int device, int n, int batch, const double* L, const do
 int dqmcb_inv_I_plus_ldr_mul_ldr(int device, int n, int batch, const double* L1, const double* d1, const double* R1,
                                  const double* L2, const double* d2, const double* R2, double* G);
 
+/* stablelinalg::inv_invldr_plus_ldr (source/stablelinalg.cpp:160-190; used by the unequal-time sweep) */
+int dqmcb_inv_invldr_plus_ldr(int device, int n, int batch, const double* L1, const double* d1, const double* R1,
+                              const double* L2, const double* d2, const double* R2, double* G);
+
+/* ---- single-proposal model calls (teacher-forced parity of source/model.cpp:109-138) ------------------ */
+/* AttractiveHubbard::local_update_ratio on the current G of every walker: R[W], delta[W] */
+int dqmcb_local_update_ratio(dqmcb_ctx* ctx, int l, int site, int new_field, double* R, double* delta);
+/* AttractiveHubbard::update_greens_local on one walker's current G */
+int dqmcb_update_greens_local(dqmcb_ctx* ctx, int walker, double delta, int site);
+/* GHQField::set_single_field (include/field.h:68-70) on the device copy */
+int dqmcb_set_single_field(dqmcb_ctx* ctx, int walker, int l, int site, int value);
+
 /* ---- per-kernel-class device timing (CUDA events on the context's stream), for bench.py's roofline ---- */
 #define DQMCB_K_PROPAGATE 0 /* wrap + Metropolis kernels */
 #define DQMCB_K_STABILIZE 1 /* Bbar + stack update + stabilised G kernels */

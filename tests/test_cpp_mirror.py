@@ -1,0 +1,122 @@
+"""The C++ host mirror (include/dqmcb/*.h: the reference's AttractiveHubbard / DQMC / update:: /
+stablelinalg:: / GF / LDRStack / GHQField surface over the C ABI), driven by a reference-style main
+(tests/cpp/host_mirror_test.cpp) and compared with the reference-generated golden fixtures.
+
+Because the mirror draws its random numbers with the reference's own libstdc++ calls, a given seed
+must reproduce the reference's trajectory: identical fields after every half sweep.
+"""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "tests", "cpp", "host_mirror_test")
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def rel(a, b):
+    a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+    return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
+
+
+def run(args, tmp_path, name="out.txt"):
+    out = str(tmp_path / name)
+    r = subprocess.run([BIN, *[str(a) for a in args], out], capture_output=True, text=True, timeout=600)
+    return r, out
+
+
+def parse(path):
+    rec = {}
+    with open(path) as f:
+        while True:
+            hdr = f.readline()
+            if not hdr:
+                break
+            name, n = hdr.split()
+            rec[name] = np.array(f.readline().split(), dtype=np.float64)
+            assert rec[name].size == int(n)
+    return rec
+
+
+def test_binary_built_and_fails_loudly_without_gpu(tmp_path):
+    assert os.path.exists(BIN), "tests/cpp/host_mirror_test missing: run __graft_entry__.build()"
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    r, _ = run(["api"], tmp_path)
+    assert r.returncode == 1 and "CUDA" in r.stderr  # no CPU fallback behind the C++ surface either
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["c0", "r7", "c1s"])
+def test_reference_style_main_reproduces_reference_trajectory(name, tmp_path):
+    g = np.load(os.path.join(GOLD, f"traj_{name}.npz"))
+    L1, L2, U, t, mu, beta, nt, n_stab, seed, n_sweeps = g["cfg"]
+    L1, L2, nt, n_stab, seed, n_sweeps = int(L1), int(L2), int(nt), int(n_stab), int(seed), int(n_sweeps)
+    n = L1 * L2
+    r, out = run(["traj", L1, L2, U, t, mu, beta, nt, n_stab, seed, n_sweeps], tmp_path)
+    assert r.returncode == 0, r.stderr
+    o = parse(out)
+    cm = lambda v: v.reshape(n, n).T  # column-major dump -> [row, col]
+    fl = lambda v: v.reshape(n, nt).T.astype(np.int64)  # imat nt x N column-major -> [l, site]
+    assert np.array_equal(fl(o["fields0"]), g["fields0"])  # GHQField ctor == reference draw order
+    assert rel(cm(o["expK"]), g["expK"]) < 1e-12  # Jacobi-eigen exp(-dtau K) vs arma::expmat
+    assert rel(cm(o["G0"]), g["G0"]) < 1e-10
+    assert abs(o["logdet0"][0] - float(g["logdet0"])) < 1e-10 * abs(float(g["logdet0"]))
+    assert abs(o["action0"][0] - float(g["action0"])) < 1e-10 * abs(float(g["action0"]))
+    assert np.allclose(o["obs0"], g["obs0"], rtol=1e-10, atol=1e-12)
+    assert rel(cm(o["corr0"]), g["corr0"]) < 1e-10
+    assert rel(cm(o["half_wrap0"]), g["half_wrap0"]) < 1e-10
+    assert rel(cm(o["stack0_prod0"]), g["stack0_prod"][0]) < 1e-9
+    for h in range(2 * n_sweeps):
+        assert np.array_equal(fl(o[f"traj_fields_{h}"]), g["traj_fields"][h]), f"fields differ after half sweep {h}"
+        assert rel(cm(o[f"traj_G_{h}"]), g["traj_G"][h]) < 1e-9
+    assert abs(o["stats"][0] - float(g["traj_acc_rate"])) < 1e-12
+    assert o["stats"][1] < 10 * float(g["traj_max_err"]) + 1e-9
+    assert abs(o["traj_action"][0] - float(g["traj_action"])) < 1e-9 * abs(float(g["traj_action"]))
+    assert abs(o["traj_logdet"][0] - g["traj_logdet"][-1]) < 1e-9 * abs(g["traj_logdet"][-1])
+    assert rel(cm(o["traj_stack_prod0"]), g["traj_stack_prod"][0]) < 1e-8
+    assert 0.0 <= o["slice_acc"][0] <= 1.0
+
+
+@pytest.mark.gpu
+def test_replica_exchange_over_local_transport(tmp_path):
+    """update::replica_exchange on the reference's 4-replica beta ladder (in-process ranks)."""
+    g = np.load(os.path.join(GOLD, "exchange.npz"))
+    r, out = run(["exchange"], tmp_path)
+    assert r.returncode == 0, r.stderr
+    o = parse(out)
+    nt, n = 16, 16
+    for a in range(2):
+        for rk in range(4):
+            f = o[f"fields_after_{a}_{rk}"].reshape(n, nt).T.astype(np.int64)
+            assert np.array_equal(f, g[f"fields_after_{a}"][rk]), f"attempt {a} rank {rk}"
+            want = g[f"logdet_after_{a}"][rk]
+            assert abs(o[f"logdet_after_{a}_{rk}"][0] - want) < 1e-9 * abs(want)
+
+
+@pytest.mark.gpu
+def test_stablelinalg_and_containers(tmp_path):
+    from oracle import dqmc_oracle as O
+
+    r, out = run(["api"], tmp_path)
+    assert r.returncode == 0, r.stderr
+    o = parse(out)
+    n = 20
+    cm = lambda v: v.reshape(n, n).T
+    M, M2 = cm(o["M"]), cm(o["M2"])
+    F, F2 = O.to_LDR(M), O.to_LDR(M2)
+    assert rel(cm(o["to_LDR_prod"]), M) < 1e-12
+    assert np.allclose(o["to_LDR_d"], F.d, rtol=1e-10)
+    assert rel(cm(o["mat_mul_ldr"]), O.mat_mul_ldr(M2, F).to_matrix()) < 1e-10
+    assert rel(cm(o["ldr_mul_mat"]), O.ldr_mul_mat(F, M2).to_matrix()) < 1e-10
+    assert rel(cm(o["ldr_mul_ldr"]), O.ldr_mul_ldr(F, F2).to_matrix()) < 1e-10
+    G, ld = O.inv_I_plus_ldr(F)
+    assert rel(cm(o["inv_I_plus_ldr"]), G) < 1e-10 and abs(o["inv_I_plus_ldr_logdet"][0] - ld) < 1e-10 * max(1, abs(ld))
+    assert rel(cm(o["inv_I_plus_ldr_mul_ldr"]), O.inv_I_plus_ldr_mul_ldr(F, F2)) < 1e-10
+    assert rel(cm(o["inv_invldr_plus_ldr"]), O.inv_invldr_plus_ldr(F, F2)) < 1e-10
+    assert list(o["exceptions"]) == [1, 1, 1, 1]
+    assert [int(x) for x in o["partner_rank_ws8_a1"]] == [O.partner_rank(r, 8, 1) for r in range(8)]

@@ -189,3 +189,58 @@ def test_stablelinalg_batched(n):
     G = capi.inv_I_plus_ldr_mul_ldr(pack(F), pack(F2))
     for i in range(b):
         assert rel_err(G[i], O.inv_I_plus_ldr_mul_ldr(F[i], F2[i])) < TOL
+
+
+@pytest.mark.parametrize("name", ["c0", "r7", "c1s"])
+def test_per_proposal_against_reference_golden(name):
+    """Rows a7/a9 one proposal at a time through the C ABI, against the reference's own numbers
+    (tests/golden, generated from oracle/_ref): R, Delta, the accept decision, then G."""
+    import os
+
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", f"traj_{name}.npz"))
+    L1, L2, U, t, mu, beta, nt, n_stab = g["cfg"][:8]
+    cfg = (int(L1), int(L2), U, t, mu, beta, int(nt), int(n_stab))
+    ctx = make_ctx(cfg, 1, g["expK"], g["invexpK"])
+    f0 = g["fields0"].astype(np.int8)
+    ctx.set_fields(f0[None])
+    ctx.set_G(g["G_wrap_fwd0"][None])
+    perm, k, u = g["tape_perm"][0], g["tape_k"][0], g["tape_u"][0]
+    f = f0[0].copy()
+    for idx in range(cfg[0] * cfg[1]):
+        i = int(perm[idx])
+        new = int(O.PROPOSAL[f[i], k[idx]])
+        R, dl = ctx.local_update_ratio(0, i, new)
+        assert abs(R[0] - g["slice0_R"][idx]) <= 1e-11 * abs(g["slice0_R"][idx])
+        assert abs(dl[0] - g["slice0_delta"][idx]) <= 1e-12 * abs(g["slice0_delta"][idx])
+        acc = bool(u[idx] < min(1.0, abs(R[0])))
+        assert acc == bool(g["slice0_accept"][idx])
+        if acc:
+            ctx.update_greens_local(0, dl[0], i)
+            ctx.set_single_field(0, 0, i, new)
+            f[i] = new
+    assert np.array_equal(ctx.get_fields()[0, 0], g["slice0_fields"])
+    assert rel_err(ctx.get_G()[0], g["slice0_G"]) < TOL
+    # and the same slice in one launch of the Metropolis kernel
+    ctx.set_fields(f0[None])
+    ctx.set_G(g["G_wrap_fwd0"][None])
+    ctx.set_tape(perm[None, None], k[None, None], u[None, None])
+    ctx.local_update(0)
+    assert np.array_equal(ctx.get_fields()[0, 0], g["slice0_fields"])
+    assert rel_err(ctx.get_G()[0], g["slice0_G"]) < TOL
+    ctx.wrap_backward(0)
+    assert rel_err(ctx.get_G()[0], g["slice0_G_wrap_bwd"]) < TOL
+
+
+def test_inv_invldr_plus_ldr():
+    from dqmc_b200 import capi
+    import os
+
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "stablelinalg.npz"))
+    for n in (12, 36):
+        p = f"n{n}_"
+        F1 = (g[p + "F1_L"], g[p + "F1_d"], g[p + "F1_R"])
+        F2 = (g[p + "F2_L"], g[p + "F2_d"], g[p + "F2_R"])
+        assert rel_err(capi.inv_invldr_plus_ldr(F1, F2)[0], g[p + "inv3_G"]) < TOL
+        assert rel_err(capi.inv_I_plus_ldr_mul_ldr(F1, F2)[0], g[p + "inv2_G"]) < TOL
+        G, ld = capi.inv_I_plus_ldr(F1)
+        assert rel_err(G[0], g[p + "inv1_G"]) < TOL and abs(ld[0] - float(g[p + "inv1_logdet"])) < 1e-10 * max(1, abs(ld[0]))

@@ -128,9 +128,11 @@ class ReplicaExchange:
             u = np.asarray(u_decider, dtype=np.float64) if u_decider is not None else self._gen.random(W)
             acc = u < prob
             verdict.copy_(torch.from_numpy(acc.astype(np.uint8)))
-            dist.send(verdict, partner, group=self.group)
+            for r in dist.batch_isend_irecv([dist.P2POp(dist.isend, verdict, partner, self.group)]):
+                r.wait()
         else:
-            dist.recv(verdict, partner, group=self.group)
+            for r in dist.batch_isend_irecv([dist.P2POp(dist.irecv, verdict, partner, self.group)]):
+                r.wait()
             acc = verdict.cpu().numpy().astype(bool)
         self.proposed += W
         self.accepted += int(acc.sum())

@@ -44,6 +44,10 @@ __global__ void __launch_bounds__(kThreads) k_propagate(Params p, int l_first, i
     double* gws = p.ws + (size_t)w * 3 * n * p.LD;
     double* g = (p.smem_mats_prop >= 1) ? tiles : gws;
     double* t = (p.smem_mats_prop >= 2) ? tiles + (size_t)n * p.LD : gws + (size_t)n * p.LD;
+    // delayed-update factors U, V (K x n each) + running diagonal, behind the resident tiles
+    double* dU = tiles + (size_t)p.smem_mats_prop * n * p.LD;
+    double* dV = dU + (size_t)p.delay_k * n;
+    double* s_diag = dV + (size_t)p.delay_k * n;
     const int ld = p.LD;
     double* Gg = p.G + (size_t)w * n * n;
     cta_copy(g, ld, Gg, n, n);
@@ -64,7 +68,10 @@ __global__ void __launch_bounds__(kThreads) k_propagate(Params p, int l_first, i
         }
         if (flags & 2) {
             load_visit_draws(p, w, visit0 + s, s_perm, s_k, s_u, s_key);
-            accepted += dev_local_update(p, n, g, ld, s_f, s_perm, s_k, s_u, s_ucol, s_vrow);
+            if (p.delay_k > 1)
+                accepted += dev_local_update_delayed(p, n, g, ld, s_f, s_perm, s_k, s_u, s_diag, dU, dV, p.delay_k);
+            else
+                accepted += dev_local_update(p, n, g, ld, s_f, s_perm, s_k, s_u, s_ucol, s_vrow);
             __syncthreads();
             for (int i = threadIdx.x; i < n; i += blockDim.x) fl[i] = s_f[i];
         }
@@ -571,9 +578,16 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
     const size_t sb = ((small_bytes(N) + 15) & ~(size_t)15);
     p.smem_mats_stab = (sb + 3 * tile <= (size_t)kMaxSmem) ? 3 : 0;
     ctx->smem_stab = sb + p.smem_mats_stab * tile;
+    p.delay_k = (cfg->delay_k > 1) ? std::min(cfg->delay_k, 64) : 0;
     const size_t pb = prop_small_bytes(N);
-    p.smem_mats_prop = (pb + 2 * tile <= (size_t)kMaxSmem) ? 2 : ((pb + tile <= (size_t)kMaxSmem) ? 1 : 0);
-    ctx->smem_prop = pb + p.smem_mats_prop * tile;
+    const size_t dly = p.delay_k ? ((size_t)2 * p.delay_k * N + N) * 8 : 0;
+    p.smem_mats_prop = (pb + dly + 2 * tile <= (size_t)kMaxSmem) ? 2 : ((pb + dly + tile <= (size_t)kMaxSmem) ? 1 : 0);
+    ctx->smem_prop = pb + dly + p.smem_mats_prop * tile;
+    if (ctx->smem_prop > (size_t)kMaxSmem) {
+        g_create_err = "delay_k too large for shared memory at this N";
+        dqmcb_destroy(ctx);
+        return DQMCB_EINVAL;
+    }
     CKC(cudaFuncSetAttribute(k_propagate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_prop));
     CKC(cudaFuncSetAttribute(k_bbar, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
     CKC(cudaFuncSetAttribute(k_stabilize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));

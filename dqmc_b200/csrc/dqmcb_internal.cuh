@@ -18,6 +18,7 @@ struct Params {
     int N, LD, nt, n_stab, n_stack, W;
     int smem_mats_prop;  // how many N x LD matrices of the propagate kernel live in SMEM (0..2)
     int smem_mats_stab;  // ... of the stabilisation kernels (0 or 3)
+    int delay_k;         // > 1: delayed rank-k Metropolis updates in the generic propagate kernel
     const double* expK;
     const double* invexpK;
     const double* expK_half;

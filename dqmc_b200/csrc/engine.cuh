@@ -359,4 +359,59 @@ __device__ int dev_local_update(const Params& p, int n, double* g, int ldg, int8
     return accepted;
 }
 
+// --------------------------------------------------------------------------------------------------
+// Delayed rank-k variant of the same loop (not in the reference, which lists it as a TODO in its
+// README; algebraically identical to the rank-1 sequence: SURVEY.md appendix A).  G = G0 + U V with
+// U (n x m), V (m x n), m <= K accepted flips pending: a proposal needs only the running diagonal;
+// an accept forms the current column / row from G0 and the pending factors (2 n m flops instead of a
+// 2 n^2 sweep over G) and G0 is touched once per K accepts by a rank-K product.  Pays off where G does
+// not sit in registers: N = 144 (G in shared memory) and N = 256 (G in L2 / HBM).
+//   dU[m*n + r] = U(r, m),  dV[m*n + c] = V(m, c),  s_diag[n] running diag(G).
+// --------------------------------------------------------------------------------------------------
+__device__ int dev_local_update_delayed(const Params& p, int n, double* g, int ldg, int8_t* s_f, const int* s_perm, const int* s_k,
+                                        const double* s_u, double* s_diag, double* dU, double* dV, int K) {
+    int accepted = 0, cnt = 0;
+    for (int t = threadIdx.x; t < n; t += blockDim.x) s_diag[t] = g[t + (size_t)t * ldg];
+    __syncthreads();
+    for (int idx = 0; idx < n; ++idx) {
+        const int i = s_perm[idx];
+        const int oldf = s_f[i];
+        const int newf = s_k[idx] + (s_k[idx] >= oldf);
+        const double gii = s_diag[i];
+        const double delta = p.lut_delta[oldf * 4 + newf];
+        const double r = 1.0 + (1.0 - gii) * delta;
+        const double R = p.lut_gb[oldf * 4 + newf] * (r * r);
+        const double prob = fmin(1.0, fabs(R));
+        if (s_u[idx] < prob) {
+            ++accepted;
+            const double pref = delta / r;
+            for (int t = threadIdx.x; t < n; t += blockDim.x) {
+                double uc = g[t + (size_t)i * ldg], vr = g[i + (size_t)t * ldg];
+                for (int m = 0; m < cnt; ++m) {
+                    uc = fma(dU[m * n + t], dV[m * n + i], uc);
+                    vr = fma(dU[m * n + i], dV[m * n + t], vr);
+                }
+                if (t == i) vr -= 1.0;
+                const double us = pref * uc;
+                dU[cnt * n + t] = us;
+                dV[cnt * n + t] = vr;
+                s_diag[t] = fma(us, vr, s_diag[t]);
+            }
+            ++cnt;
+            __syncthreads();
+            if (threadIdx.x == 0) s_f[i] = (int8_t)newf;
+            if (cnt == K) {
+                cta_gemm<true>(g, ldg, dU, 1, n, dV, n, 1, n, nullptr, nullptr, cnt);
+                cnt = 0;
+                __syncthreads();
+            }
+        }
+    }
+    if (cnt) {
+        cta_gemm<true>(g, ldg, dU, 1, n, dV, n, 1, n, nullptr, nullptr, cnt);
+        __syncthreads();
+    }
+    return accepted;
+}
+
 }  // namespace dq

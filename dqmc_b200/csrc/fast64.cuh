@@ -76,21 +76,24 @@ __device__ void f_to_ldr(const Params& p, FWork<N>& wk, double* A, double* Qo, d
     constexpr int LDT = Tile<N>::LDT;
     __syncthreads();
     DQ_PH(p, 20);
-    qrp_tile<N>(A, wk.tau, wk.jpvt, wk.vn1, wk.vn2, wk.prow);
+    qrp_tile<N>(A, wk.tau, wk.jpvt, wk.vn1, wk.sv[1], wk.sv[3]);
     DQ_PH(p, 21);
+    // column jpvt[j] of A holds R(0..j, j) (and the reflector below): d_j = |R(j,j)|, and
+    // R_final = (D^-1 R) P^T puts that column back at index jpvt[j] -- where it already is
     for (int j = threadIdx.x; j < N; j += blockDim.x) {
-        const double dj = fabs(A[j + (size_t)j * LDT]);
+        const int c = wk.jpvt[j];
+        const double dj = fabs(A[j + (size_t)c * LDT]);
         dout[j] = dj;
-        wk.vn1[j] = 1.0 / dj;
+        wk.vn2[j] = 1.0 / dj;
+        wk.ipiv[c] = j;  // step at which column c was chosen (scratch)
     }
     __syncthreads();
     for (int e = threadIdx.x; e < N * N; e += blockDim.x) {
-        const int i = e % N, j = e / N;
-        const double v = (i <= j) ? wk.vn1[i] * A[i + (size_t)j * LDT] : 0.0;
-        Ro[i + (size_t)wk.jpvt[j] * LDT] = v;
+        const int i = e % N, c = e / N;
+        Ro[i + (size_t)c * LDT] = (i <= wk.ipiv[c]) ? wk.vn2[i] * A[i + (size_t)c * LDT] : 0.0;
     }
     DQ_PH(p, 22);
-    form_q_tile<N>(Qo, A, wk.tau);
+    form_q_tile<N>(Qo, A, wk.tau, wk.jpvt);
     __syncthreads();
     DQ_PH(p, 23);
 }

@@ -14,7 +14,7 @@
 namespace dq {
 
 // development aid: set through DQMCB_PHASE_PROF=1 (see dqmcb.cu); stamps from inside the tile routines
-__device__ long long* g_dq_prof = nullptr;
+__constant__ long long* g_dq_prof = nullptr;
 #define DQ_PHG(k)                                                                    \
     do {                                                                             \
         if (g_dq_prof && blockIdx.x == 0 && (threadIdx.x & 31) == 0) g_dq_prof[k] = clock64(); \
@@ -30,6 +30,25 @@ struct Tile {
 // D(8x8) += A(8x4) * B(4x8), FP64 tensor core (SASS: DMMA.8x8x4)
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+// Index of the largest of 64 non-negative doubles (two candidates per lane: v0 at index i0 < i1 with
+// v1), lowest index on ties -- idamax semantics.  Non-negative IEEE doubles order like their bit
+// patterns, so the whole reduction is three integer REDUX instructions instead of five rounds of
+// 64-bit shuffles and FP64 compares.  Invalid candidates are passed as ok = false.
+__device__ __forceinline__ int warp_argmax2(double v0, int i0, bool ok0, double v1, int i1, bool ok1) {
+    unsigned long long k0 = ok0 ? (unsigned long long)__double_as_longlong(v0) : 0ull;
+    const unsigned long long k1 = ok1 ? (unsigned long long)__double_as_longlong(v1) : 0ull;
+    int idx = ok0 ? i0 : (ok1 ? i1 : 0x7fffffff);
+    if (ok1 && (k1 > k0 || !ok0)) {
+        k0 = k1;
+        idx = i1;
+    }
+    const unsigned hi = (unsigned)(k0 >> 32), lo = (unsigned)k0;
+    const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
+    const unsigned ml = __reduce_max_sync(0xffffffffu, (hi == mh) ? lo : 0u);
+    const int cand = (hi == mh && lo == ml) ? idx : 0x7fffffff;
+    return __reduce_min_sync(0xffffffffu, cand);
 }
 
 // Warp-level product: acc[(8 MB) x (8 NB)] += A[r0.., 0..K) * B[0..K), c0..)
@@ -217,126 +236,85 @@ __device__ __forceinline__ void tile_load_global(double* __restrict__ tile, cons
 }
 
 // ------------------------------------------------------------------------------------------------
-// Column-pivoted Householder QR (dlaqp2 semantics, see linalg.cuh::cta_qrp) for compile-time N <= 64;
-// each lane owns rows lane and lane+32 of a column.
+// Column-pivoted Householder QR, compile-time N in {32, 64}, REGISTER resident: warp q owns the
+// columns [8q, 8q+8) for the whole factorisation (lane = rows lane, lane+32: 16 doubles per lane).
 //
-// Two block barriers per column.  Warp 0 runs the serial part (partial-norm down-date of the previous
-// step for all columns at once, pivot choice, column swap, dlarfg); then all warps apply the
-// reflector to the trailing columns, each warp taking up to eight columns in two passes of four so
-// that four shuffle reductions are in flight together.  The new row-j element of every column is
-// parked in `arow` for the deferred down-date (same arithmetic as dlaqp2, executed one step later).
+//   * pivoting is implicit: columns never move; jpvt[j] = the column chosen at step j (LAPACK's
+//     jpvt) and a chosen column is frozen.  On exit column jpvt[j] of A holds R(0..j, j) in rows
+//     <= j and the Householder vector of step j below (unit diagonal implicit), tau[j] as in dgeqp3.
+//   * pivot rule: largest partial column norm |a(j:, c)|, as in dgeqp3/dlaqp2.  LAPACK tracks these
+//     norms by down-dating and recomputes them exactly whenever cancellation threatens (which, on
+//     the strongly graded matrices of the stabilisation, is most of the time); here they are simply
+//     recomputed exactly every step (one extra transposing reduction), so no safeguard logic
+//     exists.  The pivot order can differ from LAPACK's only on floating-point near-ties.
+//   * two block barriers per step; the reflector application needs no shared-memory traffic for the
+//     matrix and reduces the eight dot products of a warp with one transposing butterfly
+//     (9 shuffles instead of 40).
+// norm2[N]: squared partial norms (-1 = column already chosen); vfull[N]: dense reflector;
+// wbuf[N]: tau * (v^T a_c).
 // ------------------------------------------------------------------------------------------------
+// sum over the 32 lanes of eight per-lane values; lane l returns the total of value index
+// ((l>>4)&1)*4 + ((l>>3)&1)*2 + ((l>>2)&1)
+__device__ __forceinline__ double warp_sum8_transposed(const double (&p)[8]) {
+    const int lane = threadIdx.x & 31;
+    const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
+    double a[4], b[2];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) a[i] = (h16 ? p[4 + i] : p[i]) + __shfl_xor_sync(DQ_FULL, h16 ? p[i] : p[4 + i], 16);
+#pragma unroll
+    for (int i = 0; i < 2; ++i) b[i] = (h8 ? a[2 + i] : a[i]) + __shfl_xor_sync(DQ_FULL, h8 ? a[i] : a[2 + i], 8);
+    double c = (h4 ? b[1] : b[0]) + __shfl_xor_sync(DQ_FULL, h4 ? b[0] : b[1], 4);
+    c += __shfl_xor_sync(DQ_FULL, c, 2);
+    c += __shfl_xor_sync(DQ_FULL, c, 1);
+    return c;
+}
+
 template <int N>
-__device__ void qrp_tile(double* __restrict__ A, double* __restrict__ tau, int* __restrict__ jpvt, double* __restrict__ vn1,
-                         double* __restrict__ vn2, double* __restrict__ arow) {
-    static_assert(N <= 64, "qrp_tile holds two rows per lane");
+__device__ void qrp_tile(double* __restrict__ A, double* __restrict__ tau, int* __restrict__ jpvt, double* __restrict__ norm2,
+                         double* __restrict__ vfull, double* __restrict__ wbuf) {
+    static_assert(N == 32 || N == 64, "qrp_tile: one warp per 8-column block, two rows per lane");
     constexpr int LDT = Tile<N>::LDT;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    const double tol3z = 1.0536712127723509e-08;  // sqrt(dlamch('Epsilon'))
+    constexpr bool HB = N > 32;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int rA = lane, rB = lane + 32;
-    const bool hasB = rB < N, hasA = rA < N;
-    for (int c = warp; c < N; c += nwarps) {
-        const double x = hasA ? A[rA + (size_t)c * LDT] : 0.0, y = hasB ? A[rB + (size_t)c * LDT] : 0.0;
-        const double s = warp_sum(fma(x, x, y * y));
-        if (lane == 0) {
-            const double nr = sqrt(s);
-            vn1[c] = nr;
-            vn2[c] = nr;
-            jpvt[c] = c;
+    const int cbase = 8 * warp;
+    const bool owner = cbase < N;
+    const int mycol = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);  // see warp_sum8_transposed
+    double ca[8], cb[8];
+    unsigned done = 0;  // bit q: column cbase + q already chosen
+    if (owner) {
+        double s[8];
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const double* cp = A + (size_t)(cbase + q) * LDT;
+            ca[q] = cp[rA];
+            cb[q] = HB ? cp[rB] : 0.0;
+            s[q] = fma(ca[q], ca[q], cb[q] * cb[q]);
         }
+        const double tot = warp_sum8_transposed(s);
+        if ((lane & 3) == 0) norm2[cbase + mycol] = tot;
     }
     __syncthreads();
     for (int j = 0; j < N; ++j) {
-        double* colj = A + (size_t)j * LDT;
-        if (warp == 0) {
-            // ---- deferred down-date of step j-1 for the columns c >= j (lane: c = j + lane, j + lane + 32)
-            if (j > 0) {
-                unsigned need = 0;
+        // ---- pivot (every warp computes it: no barrier needed to publish it)
+        const int pc1 = lane + 32;
+        const double n0 = norm2[lane], n1 = HB ? norm2[pc1] : -1.0;
+        const int bi = warp_argmax2(n0, lane, n0 >= 0.0, n1, pc1, HB && n1 >= 0.0);
+        if (owner && (bi >> 3) == warp) {
+            // ---- dlarfg on rows j.. of the pivot column
+            const int qs = bi & 7;
+            double x = 0.0, y = 0.0;
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const int cc = j + lane + 32 * h;
-                    int recompute = 0;
-                    if (cc < N) {
-                        const double v1 = vn1[cc];
-                        if (v1 != 0.0) {
-                            double temp = fabs(arow[cc]) / v1;
-                            temp = fmax(1.0 - temp * temp, 0.0);
-                            const double q = v1 / vn2[cc];
-                            if (temp * (q * q) <= tol3z)
-                                recompute = 1;
-                            else
-                                vn1[cc] = v1 * sqrt(temp);
-                        }
-                    }
-                    const unsigned m = __ballot_sync(DQ_FULL, recompute);
-                    need |= m ? (1u << h) : 0u;
-                    // rare: recompute the norm of rows >= j of the flagged columns, whole warp per column
-                    unsigned mm = m;
-                    while (mm) {
-                        const int b = __ffs(mm) - 1;
-                        mm &= mm - 1;
-                        const int cr = j + b + 32 * h;
-                        const double* cp = A + (size_t)cr * LDT;
-                        const double xs = (rA >= j && hasA) ? cp[rA] : 0.0, ys = (rB >= j && hasB) ? cp[rB] : 0.0;
-                        const double nr = sqrt(warp_sum(fma(xs, xs, ys * ys)));
-                        if (lane == 0) {
-                            vn1[cr] = nr;
-                            vn2[cr] = nr;
-                        }
-                    }
-                }
-                (void)need;
-                __syncwarp();
+            for (int q = 0; q < 8; ++q) {
+                x = (q == qs) ? ca[q] : x;
+                y = (q == qs) ? cb[q] : y;
             }
-            // ---- pivot: first column of maximal partial norm among j..N-1 (idamax semantics)
-            double best = -1.0;
-            int bi = j;
-            {
-                const int c0 = j + lane, c1 = j + lane + 32;
-                if (c0 < N) {
-                    best = vn1[c0];
-                    bi = c0;
-                }
-                if (c1 < N) {
-                    const double v = vn1[c1];
-                    if (v > best) {
-                        best = v;
-                        bi = c1;
-                    }
-                }
-            }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-                const double ob = __shfl_xor_sync(DQ_FULL, best, o);
-                const int oi = __shfl_xor_sync(DQ_FULL, bi, o);
-                if (ob > best || (ob == best && oi < bi)) {
-                    best = ob;
-                    bi = oi;
-                }
-            }
-            double x = hasA ? colj[rA] : 0.0, y = hasB ? colj[rB] : 0.0;
-            if (bi != j) {
-                double* colp = A + (size_t)bi * LDT;
-                const double px = hasA ? colp[rA] : 0.0, py = hasB ? colp[rB] : 0.0;
-                if (hasA) colp[rA] = x;
-                if (hasB) colp[rB] = y;
-                x = px;
-                y = py;
-                if (lane == 0) {
-                    const int tj = jpvt[j];
-                    jpvt[j] = jpvt[bi];
-                    jpvt[bi] = tj;
-                    vn1[bi] = vn1[j];
-                    vn2[bi] = vn2[j];
-                }
-            }
-            // ---- dlarfg on rows j.. of the pivot column (held in x, y)
             const double alpha = __shfl_sync(DQ_FULL, (j < 32) ? x : y, j & 31);
-            const double xs = (rA > j) ? x : 0.0, ys = (rB > j && hasB) ? y : 0.0;
-            const double xnorm = sqrt(warp_sum(fma(xs, xs, ys * ys)));
+            const double xs = (rA > j) ? x : 0.0, ys = (HB && rB > j) ? y : 0.0;
+            const double xn2 = warp_sum(fma(xs, xs, ys * ys));
             double t = 0.0;
-            if (xnorm != 0.0) {
-                const double beta = -copysign(sqrt(fma(alpha, alpha, xnorm * xnorm)), alpha);
+            if (xn2 != 0.0) {
+                const double beta = -copysign(sqrt(fma(alpha, alpha, xn2)), alpha);
                 t = (beta - alpha) / beta;
                 const double scal = 1.0 / (alpha - beta);
                 if (rA > j) x *= scal;
@@ -344,52 +322,59 @@ __device__ void qrp_tile(double* __restrict__ A, double* __restrict__ tau, int* 
                 if (rA == j) x = beta;
                 if (rB == j) y = beta;
             }
-            if (hasA) colj[rA] = x;
-            if (hasB) colj[rB] = y;
-            if (lane == 0) tau[j] = t;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                ca[q] = (q == qs) ? x : ca[q];
+                cb[q] = (q == qs) ? y : cb[q];
+            }
+            done |= 1u << qs;
+            vfull[rA] = (rA > j) ? x : ((rA == j) ? 1.0 : 0.0);
+            if (HB) vfull[rB] = (rB > j) ? y : ((rB == j) ? 1.0 : 0.0);
+            if (lane == 0) {
+                tau[j] = t;
+                jpvt[j] = bi;
+                norm2[bi] = -1.0;
+            }
         }
         __syncthreads();
-        const double t = tau[j];
-        const double vA = (rA > j && hasA) ? colj[rA] : 0.0, vB = (rB > j && hasB) ? colj[rB] : 0.0;
-        for (int c0 = j + 1 + warp; c0 < N; c0 += 4 * nwarps) {
-            double a[4], b[4], s[4];
+        if (owner && done != 0xffu) {
+            const double t = tau[j];
+            const double vA = vfull[rA], vB = HB ? vfull[rB] : 0.0;
+            double pr[8];
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int c = c0 + q * nwarps;
-                const double* cp = A + (size_t)((c < N) ? c : c0) * LDT;
-                a[q] = hasA ? cp[rA] : 0.0;
-                b[q] = hasB ? cp[rB] : 0.0;
-                s[q] = fma(vA, a[q], vB * b[q]);
+            for (int q = 0; q < 8; ++q) pr[q] = fma(vA, ca[q], vB * cb[q]);
+            const double tot = warp_sum8_transposed(pr);
+            if ((lane & 3) == 0) wbuf[cbase + mycol] = t * tot;
+            __syncwarp();
+            double s[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const double w = ((done >> q) & 1u) ? 0.0 : wbuf[cbase + q];
+                ca[q] = fma(-w, vA, ca[q]);
+                cb[q] = fma(-w, vB, cb[q]);
+                const double ea = (rA > j) ? ca[q] : 0.0, eb = (HB && rB > j) ? cb[q] : 0.0;
+                s[q] = fma(ea, ea, eb * eb);
             }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-                for (int q = 0; q < 4; ++q) s[q] += __shfl_xor_sync(DQ_FULL, s[q], o);
-            }
-#pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int c = c0 + q * nwarps;
-                const double aj = __shfl_sync(DQ_FULL, (j < 32) ? a[q] : b[q], j & 31);
-                const double w = t * (aj + s[q]);
-                const double an = aj - w;
-                double na = fma(-w, vA, a[q]), nb = fma(-w, vB, b[q]);
-                if (rA == j) na = an;
-                if (rB == j) nb = an;
-                if (c < N) {
-                    double* cp = A + (size_t)c * LDT;
-                    if (rA >= j && hasA) cp[rA] = na;
-                    if (rB >= j && hasB) cp[rB] = nb;
-                    if (lane == 0) arow[c] = an;
-                }
-            }
+            const double n2 = warp_sum8_transposed(s);  // exact |a(j+1:, c)|^2
+            if ((lane & 3) == 0 && !((done >> mycol) & 1u)) norm2[cbase + mycol] = n2;
         }
         __syncthreads();
     }
+    if (owner) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            double* cp = A + (size_t)(cbase + q) * LDT;
+            cp[rA] = ca[q];
+            if (HB) cp[rB] = cb[q];
+        }
+    }
+    __syncthreads();
 }
 
 // Q = H_0 ... H_{N-1} explicitly (out of place), column-per-warp, barrier-free (see cta_form_q).
 template <int N>
-__device__ void form_q_tile(double* __restrict__ Q, const double* __restrict__ V, const double* __restrict__ tau) {
+__device__ void form_q_tile(double* __restrict__ Q, const double* __restrict__ V, const double* __restrict__ tau,
+                            const int* __restrict__ jpvt) {
     static_assert(N <= 64, "form_q_tile holds two rows per lane");
     constexpr int LDT = Tile<N>::LDT;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
@@ -406,7 +391,7 @@ __device__ void form_q_tile(double* __restrict__ Q, const double* __restrict__ V
         const int top = min(cb + 3, N - 1);
         for (int i = top; i >= 0; --i) {
             const double t = tau[i];
-            const double* v = V + (size_t)i * LDT;
+            const double* v = V + (size_t)jpvt[i] * LDT;  // implicit pivoting: reflector i sits in the column chosen at step i
             const double vA = (rA > i && hasA) ? v[rA] : ((rA == i) ? 1.0 : 0.0);
             const double vB = (rB > i && hasB) ? v[rB] : ((rB == i) ? 1.0 : 0.0);
             double s[4];
@@ -457,24 +442,7 @@ __device__ void lu_tile(double* __restrict__ A, int* __restrict__ ipiv, int* __r
     if (threadIdx.x == 0) *info = 0;
     for (int i = threadIdx.x; i < N; i += blockDim.x) perm[i] = i;
     if (warp == 0) {  // pivot of column 0
-        double best = hasA ? fabs(A[rA]) : -1.0;
-        int bi = rA;
-        if (hasB) {
-            const double v = fabs(A[rB]);
-            if (v > best) {
-                best = v;
-                bi = rB;
-            }
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            const double ob = __shfl_xor_sync(DQ_FULL, best, o);
-            const int oi = __shfl_xor_sync(DQ_FULL, bi, o);
-            if (ob > best || (ob == best && oi < bi)) {
-                best = ob;
-                bi = oi;
-            }
-        }
+        const int bi = warp_argmax2(hasA ? fabs(A[rA]) : 0.0, rA, hasA, hasB ? fabs(A[rB]) : 0.0, rB, hasB);
         if (lane == 0) ipiv[0] = bi;
     }
     __syncthreads();
@@ -542,24 +510,7 @@ __device__ void lu_tile(double* __restrict__ A, int* __restrict__ ipiv, int* __r
                     if (rA == j) cc[rA] = u[q];
                     if (rB == j) cc[rB] = u[q];
                     if (c == j + 1) {  // look-ahead (warp 0, first pass): pivot of the next column
-                        double best = (rA > j && hasA) ? fabs(na) : -1.0;
-                        int bi = rA;
-                        if (rB > j && hasB) {
-                            const double v = fabs(nb);
-                            if (v > best) {
-                                best = v;
-                                bi = rB;
-                            }
-                        }
-#pragma unroll
-                        for (int o = 16; o > 0; o >>= 1) {
-                            const double ob = __shfl_xor_sync(DQ_FULL, best, o);
-                            const int oi = __shfl_xor_sync(DQ_FULL, bi, o);
-                            if (ob > best || (ob == best && oi < bi)) {
-                                best = ob;
-                                bi = oi;
-                            }
-                        }
+                        const int bi = warp_argmax2(fabs(na), rA, rA > j && hasA, fabs(nb), rB, rB > j && hasB);
                         if (lane == 0) ipiv[j + 1] = bi;
                                     }
                 }
@@ -575,49 +526,49 @@ __device__ void lu_tile(double* __restrict__ A, int* __restrict__ ipiv, int* __r
 }
 
 // dgetrs 'N' in place on an N x N right-hand side: element (i, c) at Bm[i*rsB + c*csB].
-// One thread per right-hand-side column with the whole column in registers (threads 0..N-1; the
-// triangular factors are read as warp-wide broadcasts, no shuffles, no barriers).  Uses perm / rdiag
-// from lu_tile.  Caller synchronises before and after.
+// Two adjacent lanes own one right-hand-side column (even / odd rows, N/2 values each in registers;
+// threads 0..2N-1, i.e. four warps for N = 64).  The triangular factors are read as warp-wide
+// broadcasts; the only exchange per elimination step is one shuffle between the two lanes of a
+// column.  Uses perm / rdiag from lu_tile.  Caller synchronises before and after.
 template <int N>
 __device__ __noinline__ void lu_solve_tile(const double* __restrict__ A, const int* __restrict__ perm, const double* __restrict__ rdiag,
                                            double* __restrict__ Bm, int rsB, int csB) {
     static_assert(N % 2 == 0 && N <= 64, "lu_solve_tile layout");
     constexpr int LDT = Tile<N>::LDT;
-    const int c = threadIdx.x;
-    if (c >= N) return;
-    double x[N];
+    constexpr int H = N / 2;
+    const int t = threadIdx.x;
+    if (t >= 2 * N) return;  // whole warps only (2N is a multiple of 32 for N = 32, 64)
+    const int c = t >> 1, h = t & 1, lane = t & 31;
+    const int pair = lane & ~1;
+    double x[H];  // x[m] = row 2m + h
     double* col = Bm + (size_t)c * csB;
 #pragma unroll
-    for (int i = 0; i < N; ++i) x[i] = col[(size_t)perm[i] * rsB];
-    // forward: L y = P b (unit diagonal); column k of L is contiguous
+    for (int m = 0; m < H; ++m) x[m] = col[(size_t)perm[2 * m + h] * rsB];
+    // forward: L y = P b (unit diagonal)
 #pragma unroll
     for (int k = 0; k < N - 1; ++k) {
-        const double xk = x[k];
-        const double* lk = A + (size_t)k * LDT;
-        if ((k & 1) == 0) x[k + 1] = fma(-lk[k + 1], xk, x[k + 1]);
-#pragma unroll
-        for (int i = (k + 2) & ~1; i < N; i += 2) {
-            const double2 l2 = *reinterpret_cast<const double2*>(lk + i);
-            x[i] = fma(-l2.x, xk, x[i]);
-            x[i + 1] = fma(-l2.y, xk, x[i + 1]);
+        const double xk = __shfl_sync(DQ_FULL, x[k >> 1], pair | (k & 1));
+        const double* lk = A + (size_t)k * LDT + h;
+        if ((k & 1) == 0) {
+            if (h) x[k >> 1] = fma(-lk[k], xk, x[k >> 1]);  // row k+1 (odd lane)
         }
+#pragma unroll
+        for (int m = (k >> 1) + 1; m < H; ++m) x[m] = fma(-lk[2 * m], xk, x[m]);
     }
     // backward: U x = y
 #pragma unroll
     for (int k = N - 1; k >= 0; --k) {
-        const double xk = x[k] * rdiag[k];
-        x[k] = xk;
-        const double* uk = A + (size_t)k * LDT;
+        const double xk = __shfl_sync(DQ_FULL, x[k >> 1] * rdiag[k], pair | (k & 1));
+        if (h == (k & 1)) x[k >> 1] = xk;
+        const double* uk = A + (size_t)k * LDT + h;
 #pragma unroll
-        for (int i = 0; i + 1 < k; i += 2) {
-            const double2 u2 = *reinterpret_cast<const double2*>(uk + i);
-            x[i] = fma(-u2.x, xk, x[i]);
-            x[i + 1] = fma(-u2.y, xk, x[i + 1]);
+        for (int m = 0; m < (k >> 1); ++m) x[m] = fma(-uk[2 * m], xk, x[m]);
+        if (k & 1) {
+            if (!h) x[k >> 1] = fma(-uk[k - 1], xk, x[k >> 1]);  // row k-1 (even lane)
         }
-        if (k & 1) x[k - 1] = fma(-uk[k - 1], xk, x[k - 1]);
     }
 #pragma unroll
-    for (int i = 0; i < N; ++i) col[(size_t)i * rsB] = x[i];
+    for (int m = 0; m < H; ++m) col[(size_t)(2 * m + h) * rsB] = x[m];
 }
 
 }  // namespace dq

@@ -43,7 +43,7 @@ def expm_sym(A: np.ndarray) -> np.ndarray:
 class AttractiveHubbard:
     """Batched counterpart of `class AttractiveHubbard` (include/model.h:11): one model, W walkers."""
 
-    def __init__(self, L1, L2, U, t, mu, beta, nt, n_stab, n_walkers, device=0, expK=None, invexpK=None):
+    def __init__(self, L1, L2, U, t, mu, beta, nt, n_stab, n_walkers, device=0, expK=None, invexpK=None, delay_k=0):
         self.L1, self.L2, self.U, self.t, self.mu, self.beta = L1, L2, U, t, mu, beta
         self.ns_, self.nt_ = L1 * L2, nt
         self.dtau = beta / nt
@@ -54,7 +54,7 @@ class AttractiveHubbard:
         self.invexpK = expm_sym(self.dtau * K) if invexpK is None else np.asarray(invexpK)
         self.expK_half = expm_sym(-0.5 * self.dtau * K)
         self.invexpK_half = expm_sym(0.5 * self.dtau * K)
-        self.ctx = capi.Context(self.ns_, nt, n_stab, n_walkers, self.g, ETA, GAMMA, self.expK, self.invexpK, self.alpha, device)
+        self.ctx = capi.Context(self.ns_, nt, n_stab, n_walkers, self.g, ETA, GAMMA, self.expK, self.invexpK, self.alpha, device, delay_k)
         self.ctx.set_half_expK(self.expK_half, self.invexpK_half)
 
     def ns(self):

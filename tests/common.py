@@ -11,6 +11,7 @@ CONFIGS = {
     "C2s": (12, 12, 4.0, 1.0, 0.0, 2.0, 20, 5),    # 12x12, global-workspace path
     "R7": (7, 5, 3.0, 1.0, 0.2, 3.0, 23, 6),       # odd N, ragged last block (nt % n_stab != 0)
     "F32": (8, 4, 5.0, 1.0, 0.1, 2.3, 23, 5),      # N = 32 fast path, ragged last block
+    "C3s": (16, 16, 6.0, 1.0, 0.0, 1.0, 10, 5),    # 16x16 (N = 256): L2-resident tiles, DMMA generic GEMM
 }
 
 
@@ -22,14 +23,14 @@ def make_oracle(cfg, seed):
     return m, d
 
 
-def make_ctx(cfg, n_walkers, expK, invexpK, device=0):
+def make_ctx(cfg, n_walkers, expK, invexpK, device=0, delay_k=0):
     from dqmc_b200 import capi, host
 
     L1, L2, U, t, mu, beta, nt, n_stab = cfg
     import math
 
     g = math.sqrt(0.5 * abs(U) * (beta / nt))
-    return capi.Context(L1 * L2, nt, n_stab, n_walkers, g, host.ETA, host.GAMMA, expK, invexpK, -1.0, device)
+    return capi.Context(L1 * L2, nt, n_stab, n_walkers, g, host.ETA, host.GAMMA, expK, invexpK, -1.0, device, delay_k)
 
 
 def rel_err(a, b):

@@ -15,11 +15,11 @@ pytestmark = pytest.mark.gpu
 TOL = 1e-10
 
 
-def _setup(name, seeds):
+def _setup(name, seeds, delay_k=0):
     cfg = CONFIGS[name]
     pairs = [make_oracle(cfg, s) for s in seeds]
     m0 = pairs[0][0]
-    ctx = make_ctx(cfg, len(seeds), m0.expK, m0.invexpK)
+    ctx = make_ctx(cfg, len(seeds), m0.expK, m0.invexpK, delay_k=delay_k)
     for m, _ in pairs:  # all walkers share the model matrices bit-for-bit
         m.expK, m.invexpK = m0.expK, m0.invexpK
     ctx.set_fields(np.stack([m.fields for m, _ in pairs]).astype(np.int8))
@@ -48,7 +48,7 @@ def test_init_stacks_and_green(name):
             assert np.allclose(Lm[w].T @ Lm[w], np.eye(m.ns), atol=1e-12)
 
 
-@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "C2s", "F32"])
+@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "C2s", "F32", "C3s"])
 def test_wrap_steps_teacher_forced(name):
     cfg, pairs, ctx = _setup(name, [21, 22])
     rng = np.random.default_rng(5)
@@ -66,7 +66,7 @@ def test_wrap_steps_teacher_forced(name):
             assert rel_err(Gb[w], d.wrap_backward(G0[w], l)) < TOL
 
 
-@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "C2s", "F32"])
+@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "C2s", "F32", "C3s"])
 def test_block_product(name):
     cfg, pairs, ctx = _setup(name, [31, 32])
     for i in range(ctx.n_stack):
@@ -75,10 +75,10 @@ def test_block_product(name):
             assert rel_err(B[w], d.calculate_Bbar(i)) < TOL
 
 
-@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "F32"])
-def test_local_update_teacher_forced(name):
+@pytest.mark.parametrize("name,delay_k", [("C0", 0), ("C1s", 0), ("R7", 0), ("F32", 0), ("C0", 8), ("C2s", 16), ("C3s", 0), ("C3s", 32)])
+def test_local_update_teacher_forced(name, delay_k):
     """One slice of Metropolis from the oracle's G: identical decisions and fields, G to 1e-10."""
-    cfg, pairs, ctx = _setup(name, [41, 42, 43])
+    cfg, pairs, ctx = _setup(name, [41, 42, 43], delay_k)
     n, nt = pairs[0][0].ns, cfg[6]
     gens = [O.MT19937(100 + w) for w in range(len(pairs))]
     tapes = [O.rng_tape(g, n, 2) for g in gens]
@@ -102,11 +102,14 @@ def test_local_update_teacher_forced(name):
         G_prev = G
 
 
-@pytest.mark.parametrize("name,n_sweeps", [("C0", 3), ("C1s", 3), ("R7", 3), ("C2s", 1), ("F32", 3), ("C1", 1)])
-def test_trajectory(name, n_sweeps):
+@pytest.mark.parametrize("name,n_sweeps,delay_k", [("C0", 3, 0), ("C1s", 3, 0), ("R7", 3, 0), ("C2s", 1, 0), ("F32", 3, 0), ("C1", 1, 0),
+                                                   ("C3s", 1, 0), ("R7", 2, 4), ("C2s", 1, 8), ("C0", 2, 16), ("C3s", 1, 32)])
+def test_trajectory(name, n_sweeps, delay_k):
     """Free-running sweeps on the same RNG tape: identical accept decisions / fields; G compared at
-    the end of each half sweep (a stabilisation point, where G is a function of the fields only)."""
-    cfg, pairs, ctx = _setup(name, [51, 52])
+    the end of each half sweep (a stabilisation point, where G is a function of the fields only).
+    delay_k > 1 runs the delayed rank-k Metropolis update (new relative to the reference, whose
+    rank-1 sequence is its oracle: same decisions, same fields, same G)."""
+    cfg, pairs, ctx = _setup(name, [51, 52], delay_k)
     n, nt = pairs[0][0].ns, cfg[6]
     gens = [O.MT19937(200 + w) for w in range(len(pairs))]
     ctx.init_stacks()

@@ -20,7 +20,7 @@ namespace dq {
 // ---------------------------------------------------------------------------------------------------
 template <int N>
 struct StabSmem {
-    static constexpr size_t SMALL = ((size_t)(10 * N + 64) * 8 + (size_t)(2 * N + 4) * 4 + 15) & ~(size_t)15;
+    static constexpr size_t SMALL = ((size_t)(12 * N + 4 + 64) * 8 + (size_t)(2 * N + 4) * 4 + 15) & ~(size_t)15;
     static constexpr size_t BARS = 16;
     static constexpr size_t TOTAL = SMALL + BARS + 3 * Tile<N>::BYTES;
 };
@@ -28,7 +28,7 @@ struct StabSmem {
 template <int N>
 struct FWork {
     double* t[3];
-    double *tau, *vn1, *vn2, *sv[4], *dnew, *prow, *jrow, *red;
+    double *tau, *vn1, *vn2, *sv[4], *dnew, *prow, *jrow, *red, *lbuf;
     int *jpvt, *ipiv, *info;
     uint64_t* bar;
     uint32_t parity;
@@ -45,7 +45,8 @@ __device__ inline void fcarve(FWork<N>& wk, unsigned char* smem) {
     wk.prow = s + 8 * N;
     wk.jrow = s + 9 * N;
     wk.red = s + 10 * N;
-    int* ip = reinterpret_cast<int*>(s + 10 * N + 64);
+    wk.lbuf = s + 10 * N + 64;  // 2 (N + 2) doubles: double-buffered multiplier column of lu_tile
+    int* ip = reinterpret_cast<int*>(s + 12 * N + 4 + 64);
     wk.jpvt = ip;
     wk.ipiv = ip + N;
     wk.info = ip + 2 * N;
@@ -123,7 +124,7 @@ __device__ double f_inv_I_plus_ldr(const Params& p, FWork<N>& wk, const double* 
     double part = 0.0;
     for (int i = threadIdx.x; i < N; i += blockDim.x) part += (d[i] >= 1.0) ? log(d[i]) : 0.0;
     const double logdl = cta_reduce_sum(part, wk.red);  // contains barriers
-    lu_tile<N>(t1, wk.ipiv, reinterpret_cast<int*>(wk.jrow), wk.prow, wk.info);
+    lu_tile<N>(t1, reinterpret_cast<int*>(wk.jrow), wk.prow, wk.info, wk.lbuf);
     f_note_fail<N>(p, wk, 10);
     f_set_diag<N>(t2, wk.sv[0]);
     __syncthreads();
@@ -134,7 +135,7 @@ __device__ double f_inv_I_plus_ldr(const Params& p, FWork<N>& wk, const double* 
         t0[c + (size_t)r * LDT] = t2[r + (size_t)c * LDT] + L[r + (size_t)c * N] * wk.sv[1][c];
     }
     __syncthreads();
-    lu_tile<N>(t0, wk.ipiv, reinterpret_cast<int*>(wk.jrow), wk.prow, wk.info);
+    lu_tile<N>(t0, reinterpret_cast<int*>(wk.jrow), wk.prow, wk.info, wk.lbuf);
     f_note_fail<N>(p, wk, 11);
     part = 0.0;
     for (int i = threadIdx.x; i < N; i += blockDim.x) part += log(fabs(t0[i + (size_t)i * LDT]));
@@ -157,7 +158,7 @@ __device__ void f_inv_I_plus_ldr_mul_ldr(const Params& p, FWork<N>& wk, const do
     tile_load_global<N>(t0, R2);
     __syncthreads();
     DQ_PH(p, 5);
-    lu_tile<N>(t0, wk.ipiv, reinterpret_cast<int*>(wk.jrow), wk.prow, wk.info);
+    lu_tile<N>(t0, reinterpret_cast<int*>(wk.jrow), wk.prow, wk.info, wk.lbuf);
     DQ_PH(p, 6);
     f_note_fail<N>(p, wk, 12);
     f_set_diag<N>(t1, wk.sv[2]);
@@ -178,7 +179,7 @@ __device__ void f_inv_I_plus_ldr_mul_ldr(const Params& p, FWork<N>& wk, const do
     }
     __syncthreads();
     DQ_PH(p, 9);
-    lu_tile<N>(t2, wk.ipiv, reinterpret_cast<int*>(wk.jrow), wk.prow, wk.info);
+    lu_tile<N>(t2, reinterpret_cast<int*>(wk.jrow), wk.prow, wk.info, wk.lbuf);
     DQ_PH(p, 10);
     f_note_fail<N>(p, wk, 13);
     lu_solve_tile<N>(t2, reinterpret_cast<int*>(wk.jrow), wk.prow, t0, 1, LDT);  // Y (t0)

@@ -421,108 +421,108 @@ __device__ void form_q_tile(double* __restrict__ Q, const double* __restrict__ V
 }
 
 // ------------------------------------------------------------------------------------------------
-// LU with partial pivoting (dgetf2 semantics: arma::solve / arma::log_det -> dgetrf), N <= 64.
+// LU with partial pivoting (dgetf2 semantics: arma::solve / arma::log_det -> dgetrf), compile-time
+// N in {32, 64}, REGISTER resident: warp q owns the columns [8q, 8q+8) (lane = rows lane, lane+32).
 //
-// Right-looking, ONE block barrier per column, with look-ahead: in step j warp 0 updates column j+1
-// first and immediately searches its pivot (from registers), while the other warps update the rest of
-// the trailing matrix; the last warp finalises column j-1 (multipliers) and applies the row
-// interchange to the columns left of j.  Every warp handles whole columns (lane = rows lane, lane+32),
-// so the row interchange of step j is folded into the column update and needs no staging vectors.
-// Outputs besides the in-place factors: ipiv (LAPACK style), perm (perm[i] = original row now at
-// position i, i.e. the accumulated interchanges), rdiag[j] = 1 / U(j,j).
+// Row interchanges are implicit while factorising: a pivoted row is frozen where it is, `perm[j]`
+// records the row chosen at step j, and the final store writes row perm[i] to position i, which
+// yields exactly dgetrf's in-place layout (unit-lower multipliers below the diagonal, U on and above
+// it) -- same pivots, same multipliers, same arithmetic as the interchanging form.
+// ONE block barrier per step: the warp owning column j finds the pivot among the still-active rows
+// (integer REDUX argmax), publishes the multiplier column through a double-buffered shared vector,
+// and every warp applies the rank-1 update to its own register columns; the pivot-row values are
+// fetched with one shuffle per column.
+// Outputs: factors in A (dgetrf layout), perm[i] = original row at position i, rdiag[j] = 1/U(j,j),
+// ipiv is not produced (the solve uses perm).  lbuf: 2 N doubles of scratch.
 // ------------------------------------------------------------------------------------------------
 template <int N>
-__device__ void lu_tile(double* __restrict__ A, int* __restrict__ ipiv, int* __restrict__ perm, double* __restrict__ rdiag,
-                        int* __restrict__ info) {
-    static_assert(N <= 64, "lu_tile holds two rows per lane");
+__device__ void lu_tile(double* __restrict__ A, int* __restrict__ perm, double* __restrict__ rdiag, int* __restrict__ info,
+                        double* __restrict__ lbuf) {
+    static_assert(N == 32 || N == 64, "lu_tile: one warp per 8-column block, two rows per lane");
     constexpr int LDT = Tile<N>::LDT;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    constexpr bool HB = N > 32;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int rA = lane, rB = lane + 32;
-    const bool hasA = rA < N, hasB = rB < N;
+    const int cbase = 8 * warp;
+    const bool owner = cbase < N;
+    double ca[8], cb[8];
+    bool actA = true, actB = HB;  // my rows not yet chosen as pivot rows
+    int posA = 0, posB = 0;       // step at which my rows were chosen = their final position
     if (threadIdx.x == 0) *info = 0;
-    for (int i = threadIdx.x; i < N; i += blockDim.x) perm[i] = i;
-    if (warp == 0) {  // pivot of column 0
-        const int bi = warp_argmax2(hasA ? fabs(A[rA]) : 0.0, rA, hasA, hasB ? fabs(A[rB]) : 0.0, rB, hasB);
-        if (lane == 0) ipiv[0] = bi;
+    if (owner) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const double* cp = A + (size_t)(cbase + q) * LDT;
+            ca[q] = cp[rA];
+            cb[q] = HB ? cp[rB] : 0.0;
+        }
     }
-    __syncthreads();
-    int prev_p = 0;
-    double prev_rinv = 0.0, prev_jj = 0.0, prev_piv = 0.0;
+    __syncthreads();  // everybody has read A; *info initialised
     for (int j = 0; j < N; ++j) {
-        const int p = ipiv[j];
-        double* colj = A + (size_t)j * LDT;
-        const double piv = colj[p], jj = colj[j];
-        const double rinv = (piv != 0.0) ? 1.0 / piv : 0.0;
-        // multipliers of my rows after the interchange (row p now holds the old row j)
-        const double lA = (rA > j && hasA) ? ((rA == p) ? jj : colj[rA]) * rinv : 0.0;
-        const double lB = (rB > j && hasB) ? ((rB == p) ? jj : colj[rB]) * rinv : 0.0;
-        if (warp == nwarps - 1) {
-            if (j > 0) {  // finalise column j-1: U(j-1,j-1) and the multipliers below it
-                double* colq = A + (size_t)(j - 1) * LDT;
-                if (rA == j - 1) colq[rA] = prev_piv;
-                if (rB == j - 1) colq[rB] = prev_piv;
-                if (rA >= j && hasA) colq[rA] = ((rA == prev_p) ? prev_jj : colq[rA]) * prev_rinv;
-                if (rB >= j && hasB) colq[rB] = ((rB == prev_p) ? prev_jj : colq[rB]) * prev_rinv;
-                __syncwarp();
+        double* lb = lbuf + (j & 1) * (N + 2);  // [0..N-1] multipliers, [N] pivot row (as double)
+        if (owner && (j >> 3) == warp) {
+            const int qs = j & 7;
+            double x = 0.0, y = 0.0;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                x = (q == qs) ? ca[q] : x;
+                y = (q == qs) ? cb[q] : y;
             }
-            if (p != j) {  // interchange rows j and p in the columns left of j
-                for (int c = lane; c < j; c += 32) {
-                    double* cc = A + (size_t)c * LDT;
-                    const double t = cc[j];
-                    cc[j] = cc[p];
-                    cc[p] = t;
-                }
-                if (lane == 0) {
-                    const int t = perm[j];
-                    perm[j] = perm[p];
-                    perm[p] = t;
-                }
+            const int p = warp_argmax2(fabs(x), rA, actA, fabs(y), rB, actB);
+            const double piv = __shfl_sync(DQ_FULL, (p < 32) ? x : y, p & 31);
+            const double rinv = (piv != 0.0) ? 1.0 / piv : 0.0;
+            // multipliers of the rows that stay active; they are also the L entries of column j
+            const double lA = (actA && rA != p) ? x * rinv : 0.0;
+            const double lB = (actB && rB != p) ? y * rinv : 0.0;
+            lb[rA] = lA;
+            if (HB) lb[rB] = lB;
+            if (actA && rA != p) x = lA;
+            if (actB && rB != p) y = lB;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                ca[q] = (q == qs) ? x : ca[q];
+                cb[q] = (q == qs) ? y : cb[q];
             }
             if (lane == 0) {
+                lb[N] = (double)p;
+                perm[j] = p;
                 rdiag[j] = rinv;
                 if (piv == 0.0 && *info == 0) *info = j + 1;
             }
         }
-        // trailing columns: index idx = c - (j+1) goes to warp idx % nwarps, four columns per pass
-        for (int c0 = j + 1 + warp; c0 < N; c0 += 4 * nwarps) {
-            double xa[4], xb[4], u[4], vj[4];
+        __syncthreads();
+        const int p = (int)lb[N];
+        if (rA == p) {
+            actA = false;
+            posA = j;
+        }
+        if (rB == p) {
+            actB = false;
+            posB = j;
+        }
+        if (owner && cbase + 7 > j) {
+            const double lA = lb[rA], lB = HB ? lb[rB] : 0.0;  // zero for frozen rows and for row p
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int c = c0 + q * nwarps;
-                if (c < N) {
-                    const double* cc = A + (size_t)c * LDT;
-                    xa[q] = hasA ? cc[rA] : 0.0;
-                    xb[q] = hasB ? cc[rB] : 0.0;
-                    u[q] = cc[p];
-                    vj[q] = cc[j];
-                }
-            }
-            __syncwarp();  // every lane holds the old rows j and p before anyone overwrites them
-    #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                const int c = c0 + q * nwarps;
-                if (c < N) {
-                    double* cc = A + (size_t)c * LDT;
-                    const double na = fma(-lA, u[q], (rA == p) ? vj[q] : xa[q]);
-                    const double nb = fma(-lB, u[q], (rB == p) ? vj[q] : xb[q]);
-                    if (rA > j && hasA) cc[rA] = na;
-                    if (rB > j && hasB) cc[rB] = nb;
-                    if (rA == j) cc[rA] = u[q];
-                    if (rB == j) cc[rB] = u[q];
-                    if (c == j + 1) {  // look-ahead (warp 0, first pass): pivot of the next column
-                        const int bi = warp_argmax2(fabs(na), rA, rA > j && hasA, fabs(nb), rB, rB > j && hasB);
-                        if (lane == 0) ipiv[j + 1] = bi;
-                                    }
+            for (int q = 0; q < 8; ++q) {
+                const double u = __shfl_sync(DQ_FULL, (p < 32) ? ca[q] : cb[q], p & 31);
+                if (cbase + q > j) {
+                    ca[q] = fma(-lA, u, ca[q]);
+                    cb[q] = fma(-lB, u, cb[q]);
                 }
             }
         }
-        prev_p = p;
-        prev_rinv = rinv;
-        prev_jj = jj;
-        prev_piv = piv;
-        __syncthreads();
     }
-    // column N-1 needs no finalisation: its pivot is the only remaining row
+    // store in dgetrf's row order: original row r goes to position pos(r)
+    __syncthreads();
+    if (owner) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            double* cp = A + (size_t)(cbase + q) * LDT;
+            cp[posA] = ca[q];
+            if (HB) cp[posB] = cb[q];
+        }
+    }
+    __syncthreads();
 }
 
 // dgetrs 'N' in place on an N x N right-hand side: element (i, c) at Bm[i*rsB + c*csB].

@@ -139,7 +139,7 @@ def run_reference_arm(args, wl, name):
         return
     cores = os.cpu_count() or 1
     chains = cores
-    per_step = 1 if wl[0] * wl[1] >= 64 else 4
+    per_step = {36: 32, 64: 8, 144: 1, 256: 1}.get(wl[0] * wl[1], 1)  # bounded sample: the run ends within minutes
     L1, L2, U, t, mu, beta, nt, n_stab, W = wl
     from oracle import ref
 
@@ -181,7 +181,7 @@ def run_reference_arm(args, wl, name):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C1", choices=list(WORKLOADS))
@@ -235,10 +235,11 @@ def main():
         ctx.sweep_beta_to_0()
 
     # ---- kernel-resident throughput (`value`) ----
+    # product configuration: walkers split into groups on separate streams (no per-launch events)
     for _ in range(args.warmup):
         step()
     barrier()
-    ctx.timing_enable(True)
+    n_launch0 = ctx.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local_rank) as clocks:
         barrier()
@@ -249,8 +250,7 @@ def main():
             e1.record(stream)
         barrier()
     ms = e0.elapsed_time(e1)
-    kms, kn = ctx.timing_get()
-    ctx.timing_enable(False)
+    gpu_launches = ctx.launch_count() - n_launch0
     tms = torch.tensor([ms], dtype=torch.float64, device="cuda")
     if dist is not None:
         dist.all_reduce(tms, op=dist.ReduceOp.MAX)
@@ -260,6 +260,16 @@ def main():
     value = flips_per_step * args.steps / (ms_max * 1e-3)
     sweeps_per_sec = total_walkers * args.steps / (ms_max * 1e-3)
     acc, emax, emean = ctx.get_stats()
+
+    # ---- per-kernel-class launch times for the roofline: CUDA events around every launch on the
+    # launching stream (this serialises the walker groups, so it is a separate, untimed-for-`value` pass)
+    ctx.timing_enable(True)
+    n_cls = max(1, min(args.steps, 3))
+    for _ in range(n_cls):
+        step()
+    ctx.synchronize()
+    kms, kn = ctx.timing_get()
+    ctx.timing_enable(False)
 
     # ---- end to end through the C ABI with HOST buffers (`e2e`) ----
     # per step: pinned host RNG tape for the sweep (the reference's rng argument of local_update)
@@ -302,7 +312,7 @@ def main():
     peaks = measured_peaks()
     dom = int(np.argmax(kms[:2]))
     dom_name = ["propagate (wrap + Metropolis)", "stabilize (Bbar + LDR stack + G)"][dom]
-    acc_rate = float(acc.mean()) / (2.0 * (args.steps + args.warmup)) if acc.size else 0.5
+    acc_rate = float(acc.mean()) / (2.0 * (args.steps + args.warmup)) if acc.size else 0.5  # stats read before the class pass
     a = min(max(acc_rate, 0.0), 1.0)
     n3 = float(N) ** 3
     # algorithmic FP64 flops per launch: propagate launch = n_stab slices x
@@ -314,20 +324,37 @@ def main():
     avg_ms = kms[dom] / max(int(kn[dom]), 1)
     achieved = fl / (avg_ms * 1e-3) / 1e12
     peak = peaks.get("fp64_dmma_m8n8k4_tflops")
+    ncu = {}
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_summary.json")) as f:
+            ncu = json.load(f).get(args.workload, {})
+    except Exception:
+        pass
+    other = 1 - dom
+    avg_other = kms[other] / max(int(kn[other]), 1)
+    ach_other = [flops_prop, flops_stab][other] / (avg_other * 1e-3) / 1e12
+    step_flops = (flops_prop + flops_stab) * 2 * ((nt + n_stab - 1) // n_stab) * world
     roofline = {
         "bound": "tensor", "kernel": dom_name, "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-        "frac": (achieved / peak) if peak else None, "traffic": None,
-        "peak_source": "FP64 DMMA m8n8k4 peak measured on this pool's B200 by benchmarks/peaks.cu (profiles/fp64_smem_peaks.json); "
+        "frac": (achieved / peak) if peak else None,
+        "traffic": ncu.get(["propagate", "stabilize"][dom], {}).get("dram_bytes_per_launch"),
+        "peak_source": "FP64 DMMA m8n8k4 / DFMA peak measured on this pool's B200 by benchmarks/peaks.cu (profiles/fp64_smem_peaks.json); "
                        "MEASURED_PEAKS.json carries no FP64 figure",
-        "avg_launch_ms": avg_ms, "share_of_step": float(kms[dom] / max(kms.sum(), 1e-9)),
+        "avg_launch_ms": avg_ms, "share_of_step": float(kms[dom] / max(kms[:2].sum(), 1e-9)),
+        "algorithmic_flops_per_launch": fl,
         "class_ms": {"propagate": float(kms[0]), "stabilize": float(kms[1])},
+        "other_kernel": {"kernel": ["propagate (wrap + Metropolis)", "stabilize (Bbar + LDR stack + G)"][other], "achieved": ach_other,
+                         "frac": (ach_other / peak) if peak else None, "avg_launch_ms": avg_other},
+        "whole_step": {"algorithmic_tflops": step_flops / (ms_max / args.steps * 1e-3) / 1e12,
+                       "frac": (step_flops / (ms_max / args.steps * 1e-3) / 1e12 / (peak * world)) if peak else None},
+        "hbm_note": "stabilize moves 3 LDR stack entries + G per walker per launch (algorithmic %.0f MB); see traffic" % (W * (3 * (2 * N * N + N) + 2 * N * N) * 8 / 1e6),
     }
 
     cpu_baseline = None
     if not args.no_cpu_baseline:
         try:
             cores = os.cpu_count() or 1
-            ns = 2 if N >= 64 else 8
+            ns = {36: 160, 64: 40, 144: 4, 256: 1}.get(N, 4)  # ~15-30 CPU-seconds over all host threads
             v, sps, secs = cpu_reference_run(wl, cores, ns, 1)
             cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sweeps_per_sec": sps,
                             "sample": f"{cores} independent chains (one per host thread) x {ns} full sweeps of the same model, "
@@ -342,7 +369,7 @@ def main():
         "sweeps_per_sec": sweeps_per_sec, "acceptance": a, "max_wrap_err": float(emax.max()),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d) * world, "d2h_bytes_per_step": int(d2h) * world,
                 "path": "dqmcb_set_tape (pinned host RNG tape) + dqmcb_run_sweeps_host (fwd+bwd sweep, measure, fields+observables D2H)"},
-        "gpu_launches": int(kn.sum()),
+        "gpu_launches": int(gpu_launches), "walker_groups": ctx.n_groups(),
         "clocks": clocks.summary(),
         "roofline": roofline,
         "cpu_baseline": cpu_baseline,

@@ -50,7 +50,7 @@ SYMBOLS = [
     "dqmcb_run_sweeps_host", "dqmcb_to_LDR", "dqmcb_mat_mul_ldr", "dqmcb_ldr_mul_mat", "dqmcb_ldr_mul_ldr",
     "dqmcb_inv_I_plus_ldr", "dqmcb_inv_I_plus_ldr_mul_ldr", "dqmcb_partner_rank", "dqmcb_version",
     "dqmcb_timing_enable", "dqmcb_timing_get", "dqmcb_inv_invldr_plus_ldr", "dqmcb_local_update_ratio",
-    "dqmcb_update_greens_local", "dqmcb_set_single_field",
+    "dqmcb_update_greens_local", "dqmcb_set_single_field", "dqmcb_launch_count", "dqmcb_n_groups",
 ]
 
 
@@ -78,6 +78,9 @@ def lib():
         L.dqmcb_destroy.argtypes = [C.c_void_p]
         L.dqmcb_rng_mode.argtypes = [C.c_void_p, C.c_int, C.c_uint64]
         L.dqmcb_set_stream.argtypes = [C.c_void_p, C.c_void_p]
+        L.dqmcb_launch_count.restype = C.c_longlong
+        L.dqmcb_launch_count.argtypes = [C.c_void_p]
+        L.dqmcb_n_groups.argtypes = [C.c_void_p]
         L.dqmcb_update_greens_local.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int]
         L.dqmcb_local_update_ratio.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, _dp, _dp]
         L.dqmcb_set_single_field.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
@@ -252,6 +255,12 @@ class Context:
         n = np.zeros(4, dtype=np.int64)
         self._ck(self.L.dqmcb_timing_get(self.h, _d(ms), n.ctypes.data_as(C.POINTER(C.c_longlong))))
         return ms, n
+
+    def launch_count(self) -> int:
+        return int(self.L.dqmcb_launch_count(self.h))
+
+    def n_groups(self) -> int:
+        return int(self.L.dqmcb_n_groups(self.h))
 
     def set_stream(self, cuda_stream_handle: int):
         self._ck(self.L.dqmcb_set_stream(self.h, C.c_void_p(cuda_stream_handle)))

@@ -524,6 +524,8 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
     p.n_stab = cfg->n_stab;
     p.n_stack = (nt + cfg->n_stab - 1) / cfg->n_stab;
     p.W = W;
+    p.w0 = 0;
+    p.w1 = W;
     p.rng_mode = DQMCB_RNG_PHILOX;
     p.seed = 0x5DEECE66Dull;
     fill_luts(*cfg, p);
@@ -604,6 +606,20 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
         }
     }
     CKC(fast64_setup(ctx));
+    {
+        const char* gs = getenv("DQMCB_STREAMS");
+        int ng = gs ? atoi(gs) : 2;
+        ng = std::max(1, std::min(ng, 8));
+        if (W < 64 * ng || !fast64_available(ctx)) ng = 1;  // grouping only pays with many walkers per group
+        ctx->n_groups = ng;
+        if (ng > 1) {
+            for (int g = 0; g < ng; ++g) {
+                CKC(cudaStreamCreateWithFlags(&ctx->gstream[g], cudaStreamNonBlocking));
+                CKC(cudaEventCreateWithFlags(&ctx->gdone[g], cudaEventDisableTiming));
+            }
+            CKC(cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+        }
+    }
 #undef CKC
     *out = ctx;
     return DQMCB_OK;
@@ -636,6 +652,11 @@ void dqmcb_destroy(dqmcb_ctx* ctx) {
     cudaFree(ctx->d_tape_k);
     cudaFree(ctx->d_tape_u);
     cudaFree(ctx->d_mt);
+    for (int g = 0; g < 8; ++g) {
+        if (ctx->gstream[g]) cudaStreamDestroy(ctx->gstream[g]);
+        if (ctx->gdone[g]) cudaEventDestroy(ctx->gdone[g]);
+    }
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
     if (p.prof) {
         long long h[64];
         cudaDeviceSynchronize();
@@ -673,6 +694,8 @@ int dqmcb_synchronize(dqmcb_ctx* ctx) {
     return DQMCB_OK;
 }
 int dqmcb_n_stack(const dqmcb_ctx* ctx) { return ctx ? ctx->p.n_stack : -1; }
+long long dqmcb_launch_count(const dqmcb_ctx* ctx) { return ctx ? ctx->n_launches : -1; }
+int dqmcb_n_groups(const dqmcb_ctx* ctx) { return ctx ? ctx->n_groups : -1; }
 
 int dqmcb_set_half_expK(dqmcb_ctx* ctx, const double* a, const double* b) {
     NEED(ctx);
@@ -806,6 +829,7 @@ static int launch_propagate(dqmcb_ctx* ctx, int l_first, int n_slices, int dir, 
     Params p = ctx->p;
     if (p.rng_mode != DQMCB_RNG_TAPE) p.visit_base = 0;
     TimeScope ts(ctx, DQMCB_K_PROPAGATE);
+    ctx->n_launches += 1;
     if (fast64_available(ctx)) return fast64_propagate(ctx, p, l_first, n_slices, dir, v0, flags);
     k_propagate<<<p.W, kThreads, ctx->smem_prop, ctx->stream>>>(p, l_first, n_slices, dir, v0, flags);
     CK(cudaGetLastError());
@@ -815,6 +839,7 @@ static int launch_propagate(dqmcb_ctx* ctx, int l_first, int n_slices, int dir, 
 int dqmcb_init_stacks(dqmcb_ctx* ctx) {
     NEED(ctx);
     TimeScope ts(ctx, DQMCB_K_INIT);
+    ctx->n_launches += 1;
     if (fast64_available(ctx)) fast_init_stacks(ctx); else k_init_stacks<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p);
     CK(cudaGetLastError());
     ctx->stacks_ready = true;
@@ -827,6 +852,7 @@ int dqmcb_init_greenfunctions(dqmcb_ctx* ctx) {
         return DQMCB_ESTATE;
     }
     TimeScope ts(ctx, DQMCB_K_INIT);
+    ctx->n_launches += 1;
     if (fast64_available(ctx)) fast_init_green(ctx); else k_init_green<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p);
     CK(cudaGetLastError());
     ctx->green_ready = true;
@@ -872,6 +898,7 @@ int dqmcb_get_block_product(dqmcb_ctx* ctx, double* out) {
 }
 static int launch_stabilize(dqmcb_ctx* ctx, int l, int dir) {
     TimeScope ts(ctx, DQMCB_K_STABILIZE);
+    ctx->n_launches += 1;
     if (fast64_available(ctx)) fast_stabilize(ctx, l, dir); else k_stabilize<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p, l, dir);
     CK(cudaGetLastError());
     return DQMCB_OK;
@@ -887,12 +914,50 @@ int dqmcb_stabilize_backward(dqmcb_ctx* ctx, int l) {
     return launch_stabilize(ctx, l, -1);
 }
 
+// Whole half sweep with the walkers split into groups on separate streams (fast path, timing off):
+// the chains are independent, so a group's propagate -> stabilise chain only depends on itself and the
+// partial last wave of one kernel is filled by another group's kernels.  Forks from / joins to the
+// context's stream, so callers see ordinary stream semantics.
+static int grouped_sweep(dqmcb_ctx* ctx, int dir) {
+    const Params& p0 = ctx->p;
+    const int ng = ctx->n_groups;
+    unsigned long long v0 = 0;
+    if (int rc = take_visits(ctx, p0.nt, &v0)) return rc;
+    CK(cudaEventRecord(ctx->ev_fork, ctx->stream));
+    for (int g = 0; g < ng; ++g) CK(cudaStreamWaitEvent(ctx->gstream[g], ctx->ev_fork, 0));
+    for (int b = 0; b < p0.n_stack; ++b) {
+        const int i = (dir > 0) ? b : p0.n_stack - 1 - b;
+        const int l0 = i * p0.n_stab, l1 = std::min(l0 + p0.n_stab, p0.nt);
+        for (int g = 0; g < ng; ++g) {
+            Params p = p0;
+            // group boundaries at multiples of the propagate kernel's walkers per CTA
+            const int per = ((p0.W + ng - 1) / ng + dq::kPropWPC - 1) / dq::kPropWPC * dq::kPropWPC;
+            p.w0 = std::min(g * per, p0.W);
+            p.w1 = std::min(p.w0 + per, p0.W);
+            if (p.w0 >= p.w1) continue;
+            if (p.rng_mode != DQMCB_RNG_TAPE) p.visit_base = 0;
+            // visits are consumed in sweep order: slice l is visit (l) forward, (nt-1-l) backward
+            const unsigned long long vfirst = v0 + (unsigned long long)((dir > 0) ? l0 : (p0.nt - l1));
+            if (fast64_propagate(ctx, p, (dir > 0) ? l0 : l1 - 1, l1 - l0, dir, vfirst, 3, ctx->gstream[g])) return DQMCB_ECUDA;
+            fast_stabilize(ctx, (dir > 0) ? l1 - 1 : l0, dir, p.w0, p.w1, ctx->gstream[g]);
+            ctx->n_launches += 2;
+        }
+    }
+    CK(cudaGetLastError());
+    for (int g = 0; g < ng; ++g) {
+        CK(cudaEventRecord(ctx->gdone[g], ctx->gstream[g]));
+        CK(cudaStreamWaitEvent(ctx->stream, ctx->gdone[g], 0));
+    }
+    return DQMCB_OK;
+}
+
 int dqmcb_sweep_0_to_beta(dqmcb_ctx* ctx) {
     NEED(ctx);
     if (!ctx->green_ready) {
         ctx->err = "sweep before init_stacks/init_greenfunctions";
         return DQMCB_ESTATE;
     }
+    if (ctx->n_groups > 1 && !ctx->timing && fast64_available(ctx)) return grouped_sweep(ctx, +1);
     const Params& p = ctx->p;
     for (int i = 0; i < p.n_stack; ++i) {
         const int l0 = i * p.n_stab, l1 = std::min(l0 + p.n_stab, p.nt);
@@ -907,6 +972,7 @@ int dqmcb_sweep_beta_to_0(dqmcb_ctx* ctx) {
         ctx->err = "sweep before init_stacks/init_greenfunctions";
         return DQMCB_ESTATE;
     }
+    if (ctx->n_groups > 1 && !ctx->timing && fast64_available(ctx)) return grouped_sweep(ctx, -1);
     const Params& p = ctx->p;
     for (int i = p.n_stack - 1; i >= 0; --i) {
         const int l0 = i * p.n_stab, l1 = std::min(l0 + p.n_stab, p.nt);
@@ -1065,6 +1131,7 @@ int dqmcb_run_sweeps_host(dqmcb_ctx* ctx, int reinit, const int8_t* fields_in, i
     }
     if (scalars_out) {
         TimeScope ts(ctx, DQMCB_K_OTHER);
+        ctx->n_launches += 1;
         k_measure<<<p.W, kThreads, 0, ctx->stream>>>(p, ctx->d_obs, nullptr);
         CK(cudaGetLastError());
     }

@@ -19,6 +19,7 @@ struct Params {
     int smem_mats_prop;  // how many N x LD matrices of the propagate kernel live in SMEM (0..2)
     int smem_mats_stab;  // ... of the stabilisation kernels (0 or 3)
     int delay_k;         // > 1: delayed rank-k Metropolis updates in the generic propagate kernel
+    int w0, w1;          // walker range [w0, w1) of this launch (walker groups on separate streams)
     const double* expK;
     const double* invexpK;
     const double* expK_half;
@@ -79,6 +80,13 @@ struct dqmcb_ctx {
     uint32_t* d_mt = nullptr;       // [W][625] mt19937 state + index (MT19937 mode)
     size_t smem_prop = 0, smem_stab = 0;
     // optional per-launch timing
+    // walker groups: independent chains split over `n_groups` streams so that the partial last wave of
+    // one group's kernel overlaps with the other groups' kernels (DQMCB_STREAMS, default 2)
+    int n_groups = 1;
+    cudaStream_t gstream[8] = {};
+    cudaEvent_t gdone[8] = {};
+    cudaEvent_t ev_fork = nullptr;
+    long long n_launches = 0;  // kernels launched by this context so far (dqmcb_launch_count)
     bool force_generic = false;  // DQMCB_FORCE_GENERIC=1: bypass the compile-time-N fast path (parity cross-checks)
     bool timing = false;
     struct Span { cudaEvent_t a, b; int cls; };

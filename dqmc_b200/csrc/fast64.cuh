@@ -247,7 +247,7 @@ template <int N>
 __global__ void __launch_bounds__(kThreads, 2) kf_stabilize(Params p, int l, int dir) {
     extern __shared__ __align__(16) unsigned char smem[];
     constexpr int LDT = Tile<N>::LDT;
-    const int w = blockIdx.x;
+    const int w = p.w0 + blockIdx.x;
     FWork<N> wk;
     fcarve<N>(wk, smem);
     const int i = l / p.n_stab;
@@ -414,9 +414,12 @@ static inline void fast_bbar(dqmcb_ctx* ctx, int i_stack) {
     const dq::Params& p = ctx->p;
     FAST_DISPATCH(p.N, (dq::kf_bbar<FN><<<p.W, dq::kThreads, dq::StabSmem<FN>::TOTAL, ctx->stream>>>(p, i_stack)));
 }
-static inline void fast_stabilize(dqmcb_ctx* ctx, int l, int dir) {
-    const dq::Params& p = ctx->p;
-    FAST_DISPATCH(p.N, (dq::kf_stabilize<FN><<<p.W, dq::kThreads, dq::StabSmem<FN>::TOTAL, ctx->stream>>>(p, l, dir)));
+static inline void fast_stabilize(dqmcb_ctx* ctx, int l, int dir, int w0 = 0, int w1 = -1, cudaStream_t st = nullptr) {
+    dq::Params p = ctx->p;
+    p.w0 = w0;
+    p.w1 = (w1 < 0) ? p.W : w1;
+    if (!st) st = ctx->stream;
+    FAST_DISPATCH(p.N, (dq::kf_stabilize<FN><<<p.w1 - p.w0, dq::kThreads, dq::StabSmem<FN>::TOTAL, st>>>(p, l, dir)));
 }
 static inline void fast_init_stacks(dqmcb_ctx* ctx) {
     const dq::Params& p = ctx->p;
@@ -426,7 +429,9 @@ static inline void fast_init_green(dqmcb_ctx* ctx) {
     const dq::Params& p = ctx->p;
     FAST_DISPATCH(p.N, (dq::kf_init_green<FN><<<p.W, dq::kThreads, dq::StabSmem<FN>::TOTAL, ctx->stream>>>(p)));
 }
-static inline int fast64_propagate(dqmcb_ctx* ctx, const dq::Params& p, int l_first, int n_slices, int dir, unsigned long long v0, int flags) {
-    FAST_DISPATCH(p.N, dq::fast_prop_launch<FN>(ctx, p, l_first, n_slices, dir, v0, flags));
+static inline int fast64_propagate(dqmcb_ctx* ctx, const dq::Params& p, int l_first, int n_slices, int dir, unsigned long long v0, int flags,
+                                   cudaStream_t st = nullptr) {
+    if (!st) st = ctx->stream;
+    FAST_DISPATCH(p.N, dq::fast_prop_launch<FN>(st, p, l_first, n_slices, dir, v0, flags));
     return cudaGetLastError() == cudaSuccess ? DQMCB_OK : DQMCB_ECUDA;
 }

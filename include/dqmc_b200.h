@@ -63,6 +63,11 @@ const char* dqmcb_last_error(const dqmcb_ctx* ctx); /* ctx may be NULL: last cre
 int dqmcb_set_stream(dqmcb_ctx* ctx, void* cuda_stream);
 int dqmcb_synchronize(dqmcb_ctx* ctx);
 int dqmcb_n_stack(const dqmcb_ctx* ctx); /* ceil(nt / n_stab), source/dqmc.cpp:10 */
+/* kernels launched by this context so far (sweep, init and measurement kernels) */
+long long dqmcb_launch_count(const dqmcb_ctx* ctx);
+/* walker groups the sweeps are split into (independent chains on separate streams so that partial
+ * waves of one group's kernels are filled by another's; env DQMCB_STREAMS, default 2) */
+int dqmcb_n_groups(const dqmcb_ctx* ctx);
 /* half-wrap matrices exp(-/+ dtau K / 2) for dqmcb_half_wrap (source/model.cpp:34-35) */
 int dqmcb_set_half_expK(dqmcb_ctx* ctx, const double* expK_half, const double* invexpK_half);
 

@@ -247,3 +247,34 @@ def test_inv_invldr_plus_ldr():
         assert rel_err(capi.inv_I_plus_ldr_mul_ldr(F1, F2)[0], g[p + "inv2_G"]) < TOL
         G, ld = capi.inv_I_plus_ldr(F1)
         assert rel_err(G[0], g[p + "inv1_G"]) < TOL and abs(ld[0] - float(g[p + "inv1_logdet"])) < 1e-10 * max(1, abs(ld[0]))
+
+
+def test_walker_groups_on_streams_are_equivalent(monkeypatch):
+    """Splitting the independent chains into groups on separate CUDA streams (DQMCB_STREAMS) must not
+    change any walker's trajectory: same Philox keys, same kernels -> bit-identical fields and G."""
+    from dqmc_b200 import capi
+
+    cfg = CONFIGS["C1s"]
+    W = 192
+    m, _ = make_oracle(cfg, 5)
+    rng = np.random.default_rng(9)
+    f0 = rng.integers(0, 4, size=(W, cfg[6], cfg[0] * cfg[1]), dtype=np.int8)
+    out = []
+    for ng in ("1", "3"):
+        monkeypatch.setenv("DQMCB_STREAMS", ng)
+        ctx = make_ctx(cfg, W, m.expK, m.invexpK)
+        assert ctx.n_groups() == int(ng)
+        ctx.set_fields(f0)
+        ctx.rng_mode(capi.RNG_PHILOX, 77)
+        ctx.init_stacks()
+        ctx.init_greenfunctions()
+        n0 = ctx.launch_count()
+        for _ in range(2):
+            ctx.sweep_0_to_beta()
+            ctx.sweep_beta_to_0()
+        assert ctx.launch_count() - n0 == 2 * 2 * ctx.n_stack * 2 * int(ng)
+        out.append((ctx.get_fields(), ctx.get_G(), ctx.get_stats()[0]))
+        ctx.close()
+    assert np.array_equal(out[0][0], out[1][0])
+    assert np.array_equal(out[0][1], out[1][1])
+    assert np.array_equal(out[0][2], out[1][2])

@@ -187,6 +187,7 @@ def main():
     ap.add_argument("--workload", default="C1", choices=list(WORKLOADS))
     ap.add_argument("--walkers", type=int, default=0, help="override walkers per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--delay-k", type=int, default=-1, help="delayed rank-k Metropolis updates (default: 32 for N >= 128, else rank-1)")
     args = ap.parse_args()
     wl = list(WORKLOADS[args.workload])
     if args.walkers:
@@ -214,7 +215,8 @@ def main():
 
     L1, L2, U, t, mu, beta, nt, n_stab, W = wl
     N = L1 * L2
-    model = host.AttractiveHubbard(L1, L2, U, t, mu, beta, nt, n_stab, W, device=local_rank)
+    delay_k = args.delay_k if args.delay_k >= 0 else (32 if N >= 128 else 0)
+    model = host.AttractiveHubbard(L1, L2, U, t, mu, beta, nt, n_stab, W, device=local_rank, delay_k=delay_k)
     ctx = model.ctx
     stream = torch.cuda.Stream(device=local_rank)
     ctx.set_stream(stream.cuda_stream)
@@ -369,7 +371,7 @@ def main():
         "sweeps_per_sec": sweeps_per_sec, "acceptance": a, "max_wrap_err": float(emax.max()),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d) * world, "d2h_bytes_per_step": int(d2h) * world,
                 "path": "dqmcb_set_tape (pinned host RNG tape) + dqmcb_run_sweeps_host (fwd+bwd sweep, measure, fields+observables D2H)"},
-        "gpu_launches": int(gpu_launches), "walker_groups": ctx.n_groups(),
+        "gpu_launches": int(gpu_launches), "walker_groups": ctx.n_groups(), "delay_k": delay_k,
         "clocks": clocks.summary(),
         "roofline": roofline,
         "cpu_baseline": cpu_baseline,

@@ -6,7 +6,7 @@ os.environ.setdefault("DQMCB_PHASE_PROF", "1")
 from dqmc_b200 import host, capi
 W = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
 L = int(sys.argv[2]) if len(sys.argv) > 2 else 8
-m = host.AttractiveHubbard(L, L, 4.0, 1.0, 0.0, 8.0, 80, 10, W)
+m = host.AttractiveHubbard(L, L, 4.0, 1.0, 0.0, 4.0, 40, 10, W)
 m.random_fields(1)
 c = m.ctx
 c.rng_mode(capi.RNG_PHILOX, 42)

@@ -115,7 +115,9 @@ __global__ void __launch_bounds__(kThreads) k_stabilize(Params p, int l, int dir
     Work wk;
     carve(wk, p, w, p.smem_mats_stab, smem);
     const int i = l / p.n_stab;
+    DQ_PH(p, 0);
     dev_bbar(p, wk, w, i);  // -> b[0]
+    DQ_PH(p, 1);
     double *b0 = wk.b[0], *b1 = wk.b[1], *b2 = wk.b[2];
     const int l0 = wk.ld[0], l1 = wk.ld[1], l2 = wk.ld[2];
     __syncthreads();
@@ -130,7 +132,9 @@ __global__ void __launch_bounds__(kThreads) k_stabilize(Params p, int l, int dir
             store_d(wk.sv[0], stkD(p, w, i - 1), n);
             __syncthreads();
             cta_gemm<false>(b1, l1, b0, 1, l0, stkL(p, w, i - 1), 1, n, n, nullptr, wk.sv[0]);
+            DQ_PH(p, 2);
             dev_to_ldr(wk, n, b1, l1, b0, l0, b2, l2, wk.dnew);
+            DQ_PH(p, 3);
             cta_gemm<false>(stkR(p, w, i), n, b2, 1, l2, stkR(p, w, i - 1), 1, n, n, nullptr, nullptr);
             cta_copy(stkL(p, w, i), n, b0, l0, n);
         }
@@ -152,6 +156,7 @@ __global__ void __launch_bounds__(kThreads) k_stabilize(Params p, int l, int dir
     }
     store_d(stkD(p, w, i), wk.dnew, n);
     __syncthreads();  // stack entry i visible to the whole CTA (global writes + barrier)
+    DQ_PH(p, 4);
     // stabilize_GF_* (source/dqmc.cpp:148-161, 203-215)
     const double* Gnew;
     int ldn;
@@ -182,6 +187,7 @@ __global__ void __launch_bounds__(kThreads) k_stabilize(Params p, int l, int dir
         Gg[e] = v;
     }
     emax = cta_reduce_max(emax, wk.red);
+    DQ_PH(p, 13);
     if (threadIdx.x == 0) {
         p.err_max[w] = fmax(p.err_max[w], emax);
         p.err_sum[w] += emax;
@@ -579,7 +585,8 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
     const size_t tile = (size_t)N * p.LD * 8;
     const size_t sb = ((small_bytes(N) + 15) & ~(size_t)15);
     p.smem_mats_stab = (sb + 3 * tile <= (size_t)kMaxSmem) ? 3 : 0;
-    ctx->smem_stab = sb + p.smem_mats_stab * tile;
+    p.smem_stage = (p.smem_mats_stab == 0 && sb + tile <= (size_t)kMaxSmem) ? 1 : 0;
+    ctx->smem_stab = sb + (p.smem_mats_stab + p.smem_stage) * tile;
     p.delay_k = (cfg->delay_k > 1) ? std::min(cfg->delay_k, 64) : 0;
     const size_t pb = prop_small_bytes(N);
     const size_t dly = p.delay_k ? ((size_t)2 * p.delay_k * N + N) * 8 : 0;
@@ -1167,7 +1174,8 @@ static int run_ldr_op(int device, int n, int batch, int op, const double* M, con
     const size_t nn = (size_t)n * n, tile = (size_t)n * p.LD * 8;
     const size_t sb = ((small_bytes(n) + 15) & ~(size_t)15);
     p.smem_mats_stab = (sb + 3 * tile <= (size_t)kMaxSmem) ? 3 : 0;
-    const size_t smem = sb + p.smem_mats_stab * tile;
+    p.smem_stage = (p.smem_mats_stab == 0 && sb + tile <= (size_t)kMaxSmem) ? 1 : 0;
+    const size_t smem = sb + (p.smem_mats_stab + p.smem_stage) * tile;
     std::vector<void*> allocs;
     int rc = DQMCB_OK;
     auto up = [&](const double* h, size_t cnt) -> double* {

@@ -17,6 +17,8 @@ namespace dq {
 struct Work {
     double* b[3];  // N x LD tiles
     int ld[3];
+    double* stage;  // one shared-memory tile for the matrix being factorised when b[] live in global memory (N = 144)
+    int lds;
     double *tau, *vn1, *vn2, *sv[4], *dnew, *prow, *jrow, *red;
     int *jpvt, *ipiv, *info;
 };
@@ -44,6 +46,8 @@ __device__ inline void carve(Work& wk, const Params& p, int walker, int nmats_sm
     ip += N;
     wk.info = ip;
     double* tiles = reinterpret_cast<double*>(smem + ((small_bytes(N) + 15) & ~(size_t)15));
+    wk.stage = (nmats_smem == 0 && p.smem_stage) ? tiles : nullptr;
+    wk.lds = p.LD;
     double* gws = p.ws + (size_t)walker * 3 * N * p.LD;
     for (int i = 0; i < 3; ++i) {
         if (i < nmats_smem) {
@@ -81,8 +85,21 @@ __device__ inline double cta_reduce_max(double v, double* red) {
 // stablelinalg::to_LDR (source/stablelinalg.cpp:35-55).  A is factorised in place (destroyed);
 // Q -> Qo, D^-1 R P^T -> Ro (both distinct from A), |diag R| -> dout (shared vector).
 // --------------------------------------------------------------------------------------------------
+// Factorisations sweep the whole matrix once per column: when the tiles live in global memory (N = 144)
+// the matrix is first staged into the single shared-memory tile that fits.
+__device__ inline void stage_in(Work& wk, int n, double*& F, int& ldf) {
+    if (wk.stage && F != wk.stage) {
+        __syncthreads();
+        cta_copy(wk.stage, wk.lds, F, ldf, n);
+        __syncthreads();
+        F = wk.stage;
+        ldf = wk.lds;
+    }
+}
+
 __device__ void dev_to_ldr(Work& wk, int n, double* A, int lda, double* Qo, int ldq, double* Ro, int ldr, double* dout) {
     __syncthreads();
+    stage_in(wk, n, A, lda);
     cta_qrp(A, lda, n, wk.tau, wk.jpvt, wk.vn1, wk.vn2);
     for (int j = threadIdx.x; j < n; j += blockDim.x) {
         const double dj = fabs(A[j + (size_t)j * lda]);
@@ -140,11 +157,14 @@ __device__ double dev_inv_I_plus_ldr(const Params& p, Work& wk, int n, const dou
     double part = 0.0;
     for (int i = threadIdx.x; i < n; i += blockDim.x) part += (d[i] >= 1.0) ? log(d[i]) : 0.0;  // sum log D_large
     const double logdl = cta_reduce_sum(part, wk.red);
-    cta_lu(b0, l0, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    double* f0 = b0;
+    int lf0 = l0;
+    stage_in(wk, n, f0, lf0);
+    cta_lu(f0, lf0, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
     note_fail(p, wk, 10);
     set_diag(b1, l1, n, wk.sv[0]);
     __syncthreads();
-    cta_lu_solve(b0, l0, n, wk.ipiv, b1, 1, l1);  // X = R^-1 D_large^-1
+    cta_lu_solve(f0, lf0, n, wk.ipiv, b1, 1, l1);  // X = R^-1 D_large^-1
     __syncthreads();
     for (int e = threadIdx.x; e < n * n; e += blockDim.x) {  // M = X + L D_small ; b0 <- M^T
         const int r = e % n, c = e / n;
@@ -153,13 +173,16 @@ __device__ double dev_inv_I_plus_ldr(const Params& p, Work& wk, int n, const dou
         b0[c + (size_t)r * l0] = m;
     }
     __syncthreads();
-    cta_lu(b0, l0, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    f0 = b0;
+    lf0 = l0;
+    stage_in(wk, n, f0, lf0);
+    cta_lu(f0, lf0, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
     note_fail(p, wk, 11);
     part = 0.0;
-    for (int i = threadIdx.x; i < n; i += blockDim.x) part += log(fabs(b0[i + (size_t)i * l0]));
+    for (int i = threadIdx.x; i < n; i += blockDim.x) part += log(fabs(f0[i + (size_t)i * lf0]));
     const double logm = cta_reduce_sum(part, wk.red);
     // solve M^T Gt = X^T in place on X viewed transposed: the result is G column-major in b1
-    cta_lu_solve(b0, l0, n, wk.ipiv, b1, l1, 1);
+    cta_lu_solve(f0, lf0, n, wk.ipiv, b1, l1, 1);
     __syncthreads();
     return logdl + logm;
 }
@@ -176,14 +199,19 @@ __device__ void dev_inv_I_plus_ldr_mul_ldr(const Params& p, Work& wk, int n, con
     __syncthreads();
     split_d(d1, n, wk.sv[0], wk.sv[1]);
     split_d(d2, n, wk.sv[2], wk.sv[3]);
-    cta_copy(b0, l0, R2, ldg, n);
+    double* f0 = wk.stage ? wk.stage : b0;  // factorise R2 directly in the staging tile when there is one
+    int lf0 = wk.stage ? wk.lds : l0;
+    cta_copy(f0, lf0, R2, ldg, n);
     __syncthreads();
-    cta_lu(b0, l0, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    DQ_PH(p, 5);
+    cta_lu(f0, lf0, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    DQ_PH(p, 6);
     note_fail(p, wk, 12);
     set_diag(b1, l1, n, wk.sv[2]);
     __syncthreads();
-    cta_lu_solve(b0, l0, n, wk.ipiv, b1, 1, l1);  // X = R2^-1 D2_large^-1
+    cta_lu_solve(f0, lf0, n, wk.ipiv, b1, 1, l1);  // X = R2^-1 D2_large^-1
     __syncthreads();
+    DQ_PH(p, 7);
     // TermA = D1l^-1 (L1^T X)
     cta_gemm<false>(b2, l2, L1, ldg, 1, b1, 1, l1, n, wk.sv[0], nullptr);
     // b0 = L2 D2s
@@ -199,10 +227,16 @@ __device__ void dev_inv_I_plus_ldr_mul_ldr(const Params& p, Work& wk, int n, con
         b0[r + (size_t)c * l0] = rhs_mode ? wk.sv[1][r] * R1[r + (size_t)c * ldg] : wk.sv[0][r] * L1[c + (size_t)r * ldg];
     }
     __syncthreads();
-    cta_lu(b2, l2, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    double* f2 = b2;
+    int lf2 = l2;
+    stage_in(wk, n, f2, lf2);
+    DQ_PH(p, 9);
+    cta_lu(f2, lf2, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    DQ_PH(p, 10);
     note_fail(p, wk, 13);
-    cta_lu_solve(b2, l2, n, wk.ipiv, b0, 1, l0);  // Y = M^-1 RHS
+    cta_lu_solve(f2, lf2, n, wk.ipiv, b0, 1, l0);  // Y = M^-1 RHS
     __syncthreads();
+    DQ_PH(p, 11);
     cta_gemm<false>(b2, l2, b1, 1, l1, b0, 1, l0, n, nullptr, nullptr);  // G = X Y
     __syncthreads();
 }

@@ -405,13 +405,17 @@ __device__ int dev_local_update(const Params& p, int n, double* g, int ldg, int8
 __device__ int dev_local_update_delayed(const Params& p, int n, double* g, int ldg, int8_t* s_f, const int* s_perm, const int* s_k,
                                         const double* s_u, double* s_diag, double* dU, double* dV, int K) {
     int accepted = 0, cnt = 0;
-    for (int t = threadIdx.x; t < n; t += blockDim.x) s_diag[t] = g[t + (size_t)t * ldg];
+    // running diagonal, double-buffered: an accepting thread writes the other copy, so a warp that is
+    // still deciding this (or an earlier, rejected) proposal never sees a half-updated diagonal
+    double* dcur = s_diag;
+    double* dnxt = s_diag + n;
+    for (int t = threadIdx.x; t < n; t += blockDim.x) dcur[t] = g[t + (size_t)t * ldg];
     __syncthreads();
     for (int idx = 0; idx < n; ++idx) {
         const int i = s_perm[idx];
         const int oldf = s_f[i];
         const int newf = s_k[idx] + (s_k[idx] >= oldf);
-        const double gii = s_diag[i];
+        const double gii = dcur[i];
         const double delta = p.lut_delta[oldf * 4 + newf];
         const double r = 1.0 + (1.0 - gii) * delta;
         const double R = p.lut_gb[oldf * 4 + newf] * (r * r);
@@ -429,9 +433,12 @@ __device__ int dev_local_update_delayed(const Params& p, int n, double* g, int l
                 const double us = pref * uc;
                 dU[cnt * n + t] = us;
                 dV[cnt * n + t] = vr;
-                s_diag[t] = fma(us, vr, s_diag[t]);
+                dnxt[t] = fma(us, vr, dcur[t]);
             }
             ++cnt;
+            double* sw = dcur;
+            dcur = dnxt;
+            dnxt = sw;
             __syncthreads();
             if (threadIdx.x == 0) s_f[i] = (int8_t)newf;
             if (cnt == K) {

@@ -32,25 +32,6 @@ __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
-// Index of the largest of 64 non-negative doubles (two candidates per lane: v0 at index i0 < i1 with
-// v1), lowest index on ties -- idamax semantics.  Non-negative IEEE doubles order like their bit
-// patterns, so the whole reduction is three integer REDUX instructions instead of five rounds of
-// 64-bit shuffles and FP64 compares.  Invalid candidates are passed as ok = false.
-__device__ __forceinline__ int warp_argmax2(double v0, int i0, bool ok0, double v1, int i1, bool ok1) {
-    unsigned long long k0 = ok0 ? (unsigned long long)__double_as_longlong(v0) : 0ull;
-    const unsigned long long k1 = ok1 ? (unsigned long long)__double_as_longlong(v1) : 0ull;
-    int idx = ok0 ? i0 : (ok1 ? i1 : 0x7fffffff);
-    if (ok1 && (k1 > k0 || !ok0)) {
-        k0 = k1;
-        idx = i1;
-    }
-    const unsigned hi = (unsigned)(k0 >> 32), lo = (unsigned)k0;
-    const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
-    const unsigned ml = __reduce_max_sync(0xffffffffu, (hi == mh) ? lo : 0u);
-    const int cand = (hi == mh && lo == ml) ? idx : 0x7fffffff;
-    return __reduce_min_sync(0xffffffffu, cand);
-}
-
 // Warp-level product: acc[(8 MB) x (8 NB)] += A[r0.., 0..K) * B[0..K), c0..)
 //   A(r,k) at A[r*rsA + k*csA],  B(k,c) at B[k*rsB + c*csB]   (shared or global, any strides)
 // C fragment element j of block (mb, nb): row r0 + 8 mb + lane/4, col c0 + 8 nb + 2 (lane%4) + j.
@@ -253,22 +234,6 @@ __device__ __forceinline__ void tile_load_global(double* __restrict__ tile, cons
 // norm2[N]: squared partial norms (-1 = column already chosen); vfull[N]: dense reflector;
 // wbuf[N]: tau * (v^T a_c).
 // ------------------------------------------------------------------------------------------------
-// sum over the 32 lanes of eight per-lane values; lane l returns the total of value index
-// ((l>>4)&1)*4 + ((l>>3)&1)*2 + ((l>>2)&1)
-__device__ __forceinline__ double warp_sum8_transposed(const double (&p)[8]) {
-    const int lane = threadIdx.x & 31;
-    const bool h16 = lane & 16, h8 = lane & 8, h4 = lane & 4;
-    double a[4], b[2];
-#pragma unroll
-    for (int i = 0; i < 4; ++i) a[i] = (h16 ? p[4 + i] : p[i]) + __shfl_xor_sync(DQ_FULL, h16 ? p[i] : p[4 + i], 16);
-#pragma unroll
-    for (int i = 0; i < 2; ++i) b[i] = (h8 ? a[2 + i] : a[i]) + __shfl_xor_sync(DQ_FULL, h8 ? a[i] : a[2 + i], 8);
-    double c = (h4 ? b[1] : b[0]) + __shfl_xor_sync(DQ_FULL, h4 ? b[0] : b[1], 4);
-    c += __shfl_xor_sync(DQ_FULL, c, 2);
-    c += __shfl_xor_sync(DQ_FULL, c, 1);
-    return c;
-}
-
 template <int N>
 __device__ void qrp_tile(double* __restrict__ A, double* __restrict__ tau, int* __restrict__ jpvt, double* __restrict__ norm2,
                          double* __restrict__ vfull, double* __restrict__ wbuf) {

@@ -278,3 +278,32 @@ def test_walker_groups_on_streams_are_equivalent(monkeypatch):
     assert np.array_equal(out[0][0], out[1][0])
     assert np.array_equal(out[0][1], out[1][1])
     assert np.array_equal(out[0][2], out[1][2])
+
+
+def test_delayed_updates_with_tiles_in_global_memory_and_shared_sms():
+    """Delayed rank-k updates at a size where G no longer fits beside the factors in shared memory
+    (N=144, k=32: G lives in the global workspace) and with more walkers than SMs (two CTAs per SM):
+    decisions must equal the rank-1 path's, G must agree to rounding.  Regression test for a
+    write-after-read race on the running diagonal that only showed with warps far out of step."""
+    from dqmc_b200 import capi
+
+    cfg = (12, 12, 4.0, 1.0, 0.0, 1.0, 10, 5)
+    W = 296
+    m, _ = make_oracle(cfg, 5)
+    f0 = np.random.default_rng(21).integers(0, 4, size=(W, cfg[6], 144), dtype=np.int8)
+    out = []
+    for dk in (0, 32):
+        ctx = make_ctx(cfg, W, m.expK, m.invexpK, delay_k=dk)
+        ctx.set_fields(f0)
+        ctx.rng_mode(capi.RNG_PHILOX, 123)
+        ctx.init_stacks()
+        ctx.init_greenfunctions()
+        for _ in range(2):
+            ctx.sweep_0_to_beta()
+            ctx.sweep_beta_to_0()
+        out.append((ctx.get_fields(), ctx.get_G(), ctx.get_stats()))
+        ctx.close()
+    assert np.array_equal(out[0][0], out[1][0])
+    assert rel_err(out[1][1], out[0][1]) < 1e-8
+    assert np.array_equal(out[0][2][0], out[1][2][0])
+    assert out[1][2][1].max() < 1e-6

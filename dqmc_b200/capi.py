@@ -51,6 +51,8 @@ SYMBOLS = [
     "dqmcb_inv_I_plus_ldr", "dqmcb_inv_I_plus_ldr_mul_ldr", "dqmcb_partner_rank", "dqmcb_version",
     "dqmcb_timing_enable", "dqmcb_timing_get", "dqmcb_inv_invldr_plus_ldr", "dqmcb_local_update_ratio",
     "dqmcb_update_greens_local", "dqmcb_set_single_field", "dqmcb_launch_count", "dqmcb_n_groups",
+    "dqmcb_bin_configure", "dqmcb_bin_measure", "dqmcb_bin_fetch", "dqmcb_chi_site_to_chi_r", "dqmcb_chi_r_to_chi_k",
+    "dqmcb_pbc_shortest",
 ]
 
 
@@ -84,6 +86,12 @@ def lib():
         L.dqmcb_update_greens_local.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int]
         L.dqmcb_local_update_ratio.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, _dp, _dp]
         L.dqmcb_set_single_field.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int]
+        L.dqmcb_bin_configure.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.dqmcb_bin_measure.argtypes = [C.c_void_p]
+        L.dqmcb_bin_fetch.argtypes = [C.c_void_p, _dp, _dp, C.POINTER(C.c_longlong), C.c_int]
+        L.dqmcb_chi_site_to_chi_r.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, _dp, _dp]
+        L.dqmcb_chi_r_to_chi_k.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, _dp, _dp]
+        L.dqmcb_pbc_shortest.argtypes = [C.c_int, C.c_int]
         for name in ("dqmcb_synchronize", "dqmcb_init_stacks", "dqmcb_init_greenfunctions", "dqmcb_sweep_0_to_beta",
                      "dqmcb_sweep_beta_to_0", "dqmcb_reset_stats", "dqmcb_n_stack"):
             getattr(L, name).argtypes = [C.c_void_p]
@@ -274,6 +282,22 @@ class Context:
         self._ck(self.L.dqmcb_measure_equal_time(self.h, _d(sc), _d(corr)))
         return sc, (_from_cm(corr) if want_corr else None)
 
+    def bin_configure(self, L1: int, L2: int) -> None:
+        self._ck(self.L.dqmcb_bin_configure(self.h, L1, L2))
+        self._bin_shape = (L1, L2)
+
+    def bin_measure(self) -> None:
+        """MeasurementManager::measure for all W walkers (device-side accumulation, asynchronous)."""
+        self._ck(self.L.dqmcb_bin_measure(self.h))
+
+    def bin_fetch(self, reset=True):
+        """(scalar_sums[3], chi_r_sum[L1, L2], n_samples): sums since the last reset."""
+        L1, L2 = self._bin_shape
+        sc, chi = np.empty(3), np.empty(L1 * L2)
+        n = C.c_longlong(0)
+        self._ck(self.L.dqmcb_bin_fetch(self.h, _d(sc), _d(chi), C.byref(n), int(bool(reset))))
+        return sc, chi.reshape((L1, L2), order="F"), int(n.value)
+
     def global_action(self) -> np.ndarray:
         S = np.empty(self.W)
         self._ck(self.L.dqmcb_global_action(self.h, _d(S)))
@@ -380,6 +404,32 @@ def inv_invldr_plus_ldr(F1, F2, device=0):
     k = (_cm(L1), np.ascontiguousarray(d1), _cm(R1), _cm(L2), np.ascontiguousarray(d2), _cm(R2))
     _ckrc(lib().dqmcb_inv_invldr_plus_ldr(device, n, b, *[_d(x) for x in k], _d(G)))
     return _from_cm(G)
+
+
+def chi_site_to_chi_r(chi_site, L1, L2, device=0):
+    """transform::chi_site_to_chi_r on the device: chi_site [n_tau, N, N] (or [N, N]) -> [L1, L2, n_tau]."""
+    c = _b(chi_site)
+    nm = c.shape[0]
+    out = np.empty((nm, L1 * L2))
+    _ckrc(lib().dqmcb_chi_site_to_chi_r(device, L1, L2, nm, _d(_cm(c)), _d(out)))
+    return np.ascontiguousarray(out.reshape((nm, L2, L1)).transpose(2, 1, 0))
+
+
+def chi_r_to_chi_k(chi_r, L1, L2, device=0):
+    """transform::chi_r_to_chi_k on the device: chi_r [L1, L2, n_slices] -> complex [L1, L2, n_slices]."""
+    c = np.asarray(chi_r, dtype=np.float64)
+    if c.ndim == 2:
+        c = c[:, :, None]
+    nm = c.shape[2]
+    buf = np.ascontiguousarray(c.transpose(2, 1, 0))  # [slice][y][x]: x fastest = arma cube memory order
+    out = np.empty((nm, L1 * L2, 2))
+    _ckrc(lib().dqmcb_chi_r_to_chi_k(device, L1, L2, nm, _d(buf), _d(out)))
+    z = out[..., 0] + 1j * out[..., 1]
+    return np.ascontiguousarray(z.reshape((nm, L2, L1)).transpose(2, 1, 0))
+
+
+def pbc_shortest(d, L):
+    return lib().dqmcb_pbc_shortest(d, L)
 
 
 def partner_rank(rank, world_size, attempt):

@@ -15,6 +15,7 @@
 #include "dqmcb_internal.cuh"
 #include "engine.cuh"
 #include "fast64.cuh"
+#include "measure.cuh"
 
 using namespace dq;
 
@@ -654,6 +655,8 @@ void dqmcb_destroy(dqmcb_ctx* ctx) {
     cudaFree(p.err_cnt);
     cudaFree(p.fail);
     cudaFree(ctx->d_obs);
+    cudaFree(ctx->d_binpart);
+    cudaFree(ctx->d_binacc);
     cudaFree(ctx->d_scratchNN);
     cudaFree(ctx->d_tape_perm);
     cudaFree(ctx->d_tape_k);
@@ -1100,6 +1103,97 @@ int dqmcb_measure_equal_time(dqmcb_ctx* ctx, double* scalars, double* corr) {
     if (corr) CK(cudaMemcpy(corr, ctx->d_scratchNN, (size_t)p.W * p.N * p.N * 8, cudaMemcpyDeviceToHost));
     return DQMCB_OK;
 }
+// ---- measurement bins (include/measurementh5.h:189-274) -----------------------------------------------
+int dqmcb_bin_configure(dqmcb_ctx* ctx, int L1, int L2) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    if (L1 <= 0 || L2 <= 0 || L1 * L2 != p.N) {
+        ctx->err = "dqmcb_bin_configure: L1*L2 must equal n_sites";
+        return DQMCB_EINVAL;
+    }
+    const size_t len = 3 + (size_t)p.N;
+    if (!ctx->d_binpart) CK(cudaMalloc(&ctx->d_binpart, (size_t)p.W * len * 8));
+    if (!ctx->d_binacc) CK(cudaMalloc(&ctx->d_binacc, len * 8));
+    CK(cudaMemsetAsync(ctx->d_binacc, 0, len * 8, ctx->stream));
+    ctx->bin_L1 = L1;
+    ctx->bin_L2 = L2;
+    ctx->bin_samples = 0;
+    return DQMCB_OK;
+}
+int dqmcb_bin_measure(dqmcb_ctx* ctx) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    if (!ctx->d_binacc) {
+        ctx->err = "dqmcb_bin_measure: call dqmcb_bin_configure first";
+        return DQMCB_ESTATE;
+    }
+    const int len = 3 + p.N;
+    {
+        TimeScope ts(ctx, DQMCB_K_OTHER);
+        k_bin_measure<<<p.W, kThreads, 0, ctx->stream>>>(p, ctx->bin_L1, ctx->bin_L2, ctx->d_binpart);
+        k_bin_reduce<<<(len + 127) / 128, 128, 0, ctx->stream>>>(p.W, len, ctx->d_binpart, ctx->d_binacc);
+    }
+    ctx->n_launches += 2;
+    CK(cudaGetLastError());
+    ctx->bin_samples += p.W;
+    return DQMCB_OK;
+}
+int dqmcb_bin_fetch(dqmcb_ctx* ctx, double* scalar_sums, double* chi_r_sum, long long* n_samples, int reset) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    if (!ctx->d_binacc) {
+        ctx->err = "dqmcb_bin_fetch: call dqmcb_bin_configure first";
+        return DQMCB_ESTATE;
+    }
+    const size_t len = 3 + (size_t)p.N;
+    std::vector<double> h(len);
+    CK(cudaMemcpyAsync(h.data(), ctx->d_binacc, len * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (scalar_sums)
+        for (int k = 0; k < 3; ++k) scalar_sums[k] = h[k];
+    if (chi_r_sum)
+        for (int k = 0; k < p.N; ++k) chi_r_sum[k] = h[3 + k];
+    if (n_samples) *n_samples = ctx->bin_samples;
+    if (reset) {
+        CK(cudaMemsetAsync(ctx->d_binacc, 0, len * 8, ctx->stream));
+        ctx->bin_samples = 0;
+    }
+    return DQMCB_OK;
+}
+
+// stand-alone transforms on host buffers (transform::chi_site_to_chi_r / chi_r_to_chi_k)
+static int run_transform(int device, int L1, int L2, int n_mats, const double* in, size_t in_per, double* out, size_t out_per,
+                         int which) {
+    if (L1 <= 0 || L2 <= 0 || n_mats < 0 || (n_mats > 0 && (!in || !out))) return DQMCB_EINVAL;
+    if (n_mats == 0) return DQMCB_OK;
+    if (cudaSetDevice(device) != cudaSuccess) return DQMCB_ECUDA;
+    double *d_in = nullptr, *d_out = nullptr;
+    int rc = DQMCB_OK;
+    if (cudaMalloc(&d_in, in_per * n_mats * 8) != cudaSuccess || cudaMalloc(&d_out, out_per * n_mats * 8) != cudaSuccess) rc = DQMCB_ECUDA;
+    if (rc == DQMCB_OK && cudaMemcpy(d_in, in, in_per * n_mats * 8, cudaMemcpyHostToDevice) != cudaSuccess) rc = DQMCB_ECUDA;
+    if (rc == DQMCB_OK) {
+        if (which == 0)
+            k_chi_site_to_chi_r<<<n_mats, 128>>>(L1, L2, d_in, d_out);
+        else
+            k_chi_r_to_chi_k<<<n_mats, 128>>>(L1, L2, d_in, d_out);
+        if (cudaGetLastError() != cudaSuccess || cudaDeviceSynchronize() != cudaSuccess) rc = DQMCB_ECUDA;
+    }
+    if (rc == DQMCB_OK && cudaMemcpy(out, d_out, out_per * n_mats * 8, cudaMemcpyDeviceToHost) != cudaSuccess) rc = DQMCB_ECUDA;
+    cudaFree(d_in);
+    cudaFree(d_out);
+    if (rc != DQMCB_OK) g_create_err = "dqmcb transform: CUDA failure (no device?)";
+    return rc;
+}
+int dqmcb_chi_site_to_chi_r(int device, int L1, int L2, int n_mats, const double* chi_site, double* chi_r) {
+    const size_t n = (size_t)L1 * L2;
+    return run_transform(device, L1, L2, n_mats, chi_site, n * n, chi_r, n, 0);
+}
+int dqmcb_chi_r_to_chi_k(int device, int L1, int L2, int n_mats, const double* chi_r, double* chi_k) {
+    const size_t n = (size_t)L1 * L2;
+    return run_transform(device, L1, L2, n_mats, chi_r, n, chi_k, 2 * n, 1);
+}
+int dqmcb_pbc_shortest(int d, int L) { return dq::pbc_shortest(d, L); }
+
 int dqmcb_global_action(dqmcb_ctx* ctx, double* S) {
     NEED(ctx);
     const Params& p = ctx->p;

@@ -79,6 +79,11 @@ struct dqmcb_ctx {
     double* d_obs = nullptr;  // [W][4]
     double* d_scratchNN = nullptr;  // [W][N*N] for measurement outputs
     uint32_t* d_mt = nullptr;       // [W][625] mt19937 state + index (MT19937 mode)
+    // measurement bin on the device (dqmcb_bin_*): per-walker vectors and the running sums
+    int bin_L1 = 0, bin_L2 = 0;
+    double* d_binpart = nullptr;    // [W][3 + N]
+    double* d_binacc = nullptr;     // [3 + N]
+    long long bin_samples = 0;
     size_t smem_prop = 0, smem_stab = 0;
     // optional per-launch timing
     // walker groups: independent chains split over `n_groups` streams so that the partial last wave of

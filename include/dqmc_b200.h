@@ -126,6 +126,28 @@ void* dqmcb_device_ptr(dqmcb_ctx* ctx, int which);
 /* Observables::calculate_{density,doubleOccupancy,swavePairing,densityCorr} (source/model.cpp:167-288)
  * from the current G: scalars[W][3], corr[W][N*N] (may be NULL). */
 int dqmcb_measure_equal_time(dqmcb_ctx* ctx, double* scalars, double* corr);
+/* ---- measurement bins on the device (include/measurementh5.h) ------------------------------------------
+ * MeasurementManager::measure (:189-229) / accumulate (:231-274) for the observables source/main.cpp:116-119
+ * registers (density, doubleOcc, swave, densityCorr), for all W walkers at once and without leaving the
+ * device: each measure adds W samples to the bin; the correlation is accumulated already folded onto
+ * displacements (transform::chi_site_to_chi_r, :20-66 -- the fold is linear), so a bin is 3 + L1*L2 doubles.
+ * Lattice as source/main.cpp:84-88 (a1=(1,0), a2=(0,1), one orbital, site = uy*L1 + ux). */
+int dqmcb_bin_configure(dqmcb_ctx* ctx, int L1, int L2);  /* L1*L2 == n_sites; clears the bin */
+int dqmcb_bin_measure(dqmcb_ctx* ctx);                    /* asynchronous on the context's stream */
+/* SUMS over the samples since the last reset (divide by *n_samples; sums add across ranks):
+ * scalar_sums[3] = density, doubleOcc, swave; chi_r_sum[L1*L2], element (bx,by) at bx + L1*by, the
+ * memory order of the arma::cube the reference writes.  Any pointer may be NULL. */
+int dqmcb_bin_fetch(dqmcb_ctx* ctx, double* scalar_sums, double* chi_r_sum, long long* n_samples, int reset);
+/* transform::chi_site_to_chi_r (include/measurementh5.h:20-66) for n_mats column-major N x N matrices
+ * (the slices of the reference's cube; host buffers): chi_r[n_mats][L1*L2]. */
+int dqmcb_chi_site_to_chi_r(int device, int L1, int L2, int n_mats, const double* chi_site, double* chi_r);
+/* transform::chi_r_to_chi_k (include/measurementh5.h:78-116), k-points of include/lattice.h:36-49:
+ * chi_k[n_mats][L1*L2][2] (re, im), element (kx,ky) at kx + L1*ky.  For L1 != L2 the reference indexes
+ * its output out of bounds; k-point (n, m) is stored at (n, m) here, identical for L1 == L2. */
+int dqmcb_chi_r_to_chi_k(int device, int L1, int L2, int n_mats, const double* chi_r, double* chi_k);
+/* transform::pbc_shortest (include/measurementh5.h:13-17); host arithmetic, needs no device */
+int dqmcb_pbc_shortest(int d, int L);
+
 /* AttractiveHubbard::global_action, source/model.cpp:140-159: S[W] */
 int dqmcb_global_action(dqmcb_ctx* ctx, double* S);
 /* DQMC::half_warp, equal-time entry (source/dqmc.cpp:288-315): Gsym[W][N*N] = invexpKhalf G expKhalf */

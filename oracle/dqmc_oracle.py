@@ -470,6 +470,108 @@ def observables(G: np.ndarray):
 
 
 # ----------------------------------------------------------------------------------------------
+# Measurement pipeline -- include/measurementh5.h (transform:: :12-117, MeasurementManager :120-361)
+# and the k-points of include/lattice.h:36-49 (square lattice a1=(1,0), a2=(0,1), one orbital, as
+# source/main.cpp:84-88 sets it up)
+# ----------------------------------------------------------------------------------------------
+def pbc_shortest(d: int, L: int) -> int:  # include/measurementh5.h:13-17 (C++ int division)
+    if d > L // 2:
+        d -= L
+    if d <= -(L // 2):
+        d += L
+    return d
+
+
+def chi_site_to_chi_r(chi_site: np.ndarray, L1: int, L2: int) -> np.ndarray:
+    """include/measurementh5.h:20-66 for n_orb = 1: chi_site [n_tau, N, N] (or [N, N]) indexed
+    (tau, i, j) -> chi_r [L1, L2, n_tau], bin (dx + L1/2 - 1, dy + L2/2 - 1) of the shortest
+    displacement cell_j - cell_i, each entry divided by n_cells."""
+    c = np.asarray(chi_site, dtype=np.float64)
+    if c.ndim == 2:
+        c = c[None]
+    nt, n = c.shape[0], L1 * L2
+    out = np.zeros((L1, L2, nt))
+    for i in range(n):
+        cxi, cyi = i % L1, i // L1
+        for j in range(n):
+            cxj, cyj = j % L1, j // L1
+            dx = pbc_shortest(cxj - cxi, L1) + L1 // 2 - 1
+            dy = pbc_shortest(cyj - cyi, L2) + L2 // 2 - 1
+            out[dx, dy, :] += c[:, i, j] / n
+    return out
+
+
+def k_points(L1: int, L2: int) -> np.ndarray:  # include/lattice.h:36-49, a1=(1,0), a2=(0,1)
+    b1 = np.array([2 * np.pi / L1, 0.0])
+    b2 = np.array([0.0, 2 * np.pi / L2])
+    pts = []
+    for n in range(L1):
+        qx = n - L1 // 2 + 1
+        for m in range(L2):
+            qy = m - L2 // 2 + 1
+            pts.append(qx * b1 + qy * b2)
+    return np.array(pts)
+
+
+def chi_r_to_chi_k(chi_r: np.ndarray, L1: int, L2: int) -> np.ndarray:
+    """include/measurementh5.h:78-116: chi_k[kx, ky, t] = sum_r chi_r[x, y, t] exp(-i k.r).
+    The reference stores k-point kidx = n*L2 + m at (kidx / L1, kidx % L2), which is (n, m) only for
+    L1 == L2 and indexes out of bounds otherwise (undefined behaviour there); this restatement uses
+    (n, m) and is therefore pinned on square lattices."""
+    c = np.asarray(chi_r, dtype=np.float64)
+    if c.ndim == 2:
+        c = c[:, :, None]
+    nx, ny, nt = c.shape
+    kp = k_points(L1, L2)
+    x = np.arange(nx) - (L1 // 2 - 1)
+    y = np.arange(ny) - (L2 // 2 - 1)
+    out = np.zeros((L1, L2, nt), dtype=np.complex128)
+    for kidx in range(L1 * L2):
+        phase = kp[kidx, 0] * x[:, None] + kp[kidx, 1] * y[None, :]
+        w = np.cos(phase) - 1j * np.sin(phase)
+        out[kidx // L2, kidx % L2, :] = np.tensordot(w, c, axes=([0, 1], [0, 1]))
+    return out
+
+
+class MeasurementManager:
+    """include/measurementh5.h:120-361 wired as source/main.cpp:114-119 (density, doubleOcc, swave,
+    densityCorr).  `datasets` collects what the reference writes per bin: /bin_<n>/scalar/<name> [1],
+    /bin_<n>/equaltime/densityCorr [L1, L2, 1], /binK_<n>/equaltime/densityCorr [L1, L2, 1, 2]."""
+
+    SCALARS = ("density", "doubleOcc", "swave")
+
+    def __init__(self, L1: int, L2: int):
+        self.L1, self.L2 = L1, L2
+        self.bin = 0
+        self.datasets: dict = {}
+        self._reset()
+
+    def _reset(self):
+        self.scal = np.zeros(3)
+        self.corr = None
+        self.count = 0
+
+    def measure(self, G: np.ndarray) -> None:  # :189-229
+        d, o, s, corr = observables(G)
+        self.scal += (d, o, s)
+        self.corr = corr.copy() if self.corr is None else self.corr + corr
+        self.count += 1
+
+    def accumulate(self) -> None:  # :231-274 + saveToHDF5 :276-361
+        scal = self.scal / self.count if self.count else self.scal
+        b = self.bin
+        for name, v in zip(self.SCALARS, scal):
+            self.datasets[f"/bin_{b}/scalar/{name}"] = np.array([v])
+        if self.corr is not None:
+            chi_r = chi_site_to_chi_r(self.corr / self.count, self.L1, self.L2)
+            chi_k = chi_r_to_chi_k(chi_r, self.L1, self.L2)
+            self.datasets[f"/bin_{b}/equaltime/densityCorr"] = chi_r
+            self.datasets[f"/binK_{b}/equaltime/densityCorr"] = np.stack([chi_k.real, chi_k.imag], axis=-1)
+        self._reset()
+        self.bin += 1
+
+
+# ----------------------------------------------------------------------------------------------
 # Replica exchange -- source/update.cpp:47-117, all replicas in one process
 # ----------------------------------------------------------------------------------------------
 def replica_exchange(sims: list[DQMC], attempt: int, u_decider: dict[int, float]):

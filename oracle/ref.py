@@ -324,3 +324,78 @@ def run_sweeps(sims: list[RefSim], n_sweeps: int) -> float:
     """Times n_sweeps full sweeps on every chain, one host thread per chain.  Returns seconds."""
     arr = (C.c_void_p * len(sims))(*[s.h for s in sims])
     return lib().ref_run_sweeps(arr, len(sims), n_sweeps)
+
+
+class RefMeasure:
+    """The reference's MeasurementManager + transform:: functions (include/measurementh5.h), compiled
+    unmodified over the HDF5 recorder shim (oracle/ref_measure.cpp).  `datasets()` returns what
+    results/data_<rank>.h5 would contain: {path: ndarray with the dataset's dims, C order}."""
+
+    def __init__(self, L1: int, L2: int, rank: int = 0):
+        L = lib()
+        L.refm_create.restype = C.c_void_p
+        L.refm_create.argtypes = [C.c_int, C.c_int, C.c_int]
+        for name in ("refm_destroy", "refm_accumulate"):
+            getattr(L, name).argtypes = [C.c_void_p]
+        L.refm_measure.argtypes = [C.c_void_p, _dp]
+        L.refm_dataset_info.argtypes = [C.c_int, C.c_char_p, C.c_int, _llp, _ip]
+        L.refm_dataset_data.argtypes = [C.c_int, _dp]
+        L.refm_file_name.argtypes = [C.c_char_p, C.c_int]
+        L.refm_chi_site_to_chi_r.argtypes = [C.c_void_p, C.c_int, _dp, _dp]
+        L.refm_chi_r_to_chi_k.argtypes = [C.c_void_p, C.c_int, _dp, _dp]
+        self.L, self.L1, self.L2, self.N = L, L1, L2, L1 * L2
+        self.h = L.refm_create(L1, L2, rank)
+        if not self.h:
+            raise RuntimeError("refm_create failed")
+
+    def close(self):
+        if self.h:
+            self.L.refm_destroy(self.h)
+            self.h = None
+
+    def measure(self, G: np.ndarray) -> None:
+        g = np.asfortranarray(G, dtype=np.float64)  # arma::mat is column-major
+        self.L.refm_measure(self.h, g.ctypes.data_as(_dp))
+
+    def accumulate(self) -> None:
+        self.L.refm_accumulate(self.h)
+
+    def file_name(self) -> str:
+        buf = C.create_string_buffer(512)
+        self.L.refm_file_name(buf, 512)
+        return buf.value.decode()
+
+    def datasets(self) -> dict:
+        out = {}
+        for i in range(self.L.refm_n_datasets()):
+            path = C.create_string_buffer(512)
+            dims = (C.c_longlong * 4)()
+            rank = C.c_int()
+            n = self.L.refm_dataset_info(i, path, 512, dims, C.byref(rank))
+            data = np.empty(n, dtype=np.float64)
+            self.L.refm_dataset_data(i, data.ctypes.data_as(_dp))
+            out[path.value.decode()] = data.reshape([int(dims[k]) for k in range(rank.value)])
+        return out
+
+    def chi_site_to_chi_r(self, chi_site: np.ndarray) -> np.ndarray:
+        """chi_site [n_tau, N, N] (row i, col j) -> arma cube (L1, L2, n_tau) returned as [dx, dy, slice]."""
+        c = np.asarray(chi_site, dtype=np.float64)
+        if c.ndim == 2:
+            c = c[None]
+        nt = c.shape[0]
+        buf = np.ascontiguousarray(np.stack([np.asfortranarray(s).ravel(order="F") for s in c]))
+        out = np.empty(self.L1 * self.L2 * nt, dtype=np.float64)
+        self.L.refm_chi_site_to_chi_r(self.h, nt, buf.ctypes.data_as(_dp), out.ctypes.data_as(_dp))
+        return out.reshape((self.L1, self.L2, nt), order="F")
+
+    def chi_r_to_chi_k(self, chi_r: np.ndarray) -> np.ndarray:
+        """chi_r [L1, L2, n_slices] -> complex [L1, L2, n_slices]."""
+        c = np.asfortranarray(chi_r, dtype=np.float64)
+        nt = c.shape[2]
+        out = np.empty(2 * c.size, dtype=np.float64)
+        self.L.refm_chi_r_to_chi_k(self.h, nt, c.ravel(order="F").ctypes.data_as(_dp), out.ctypes.data_as(_dp))
+        z = out[0::2] + 1j * out[1::2]
+        return z.reshape((self.L1, self.L2, nt), order="F")
+
+    def pbc_shortest(self, d: int, L: int) -> int:
+        return int(self.L.refm_pbc_shortest(d, L))

@@ -175,6 +175,46 @@ def exchange_case():
     np.savez_compressed(os.path.join(HERE, "exchange.npz"), **out)
 
 
+def measure_case():
+    """The reference's measurement pipeline (include/measurementh5.h) on G's of a real trajectory:
+    MeasurementManager wired as source/main.cpp:114-119, 2 bins x 4 measurements on the 6x6 lattice,
+    datasets as the HDF5 recorder shim saw them; stand-alone transforms on random cubes (square 6x6,
+    odd 5x5 and, for the fold only, 4x6 -- chi_r_to_chi_k of the reference indexes out of bounds there)."""
+    out = {}
+    L1 = L2 = 6
+    sim = ref.RefSim(L1, L2, 4.0, 1.0, -0.1, 2.0, 20, 5, 77)
+    mm = ref.RefMeasure(L1, L2, rank=2)
+    Gs = []
+    for b in range(2):
+        for _ in range(4):
+            sim.sweep_fwd()
+            sim.sweep_bwd()
+            G = sim.G(0)
+            Gs.append(G)
+            mm.measure(G)
+        mm.accumulate()
+    out["G"] = np.stack(Gs)
+    out["file_name"] = np.array(mm.file_name())
+    ds = mm.datasets()
+    out["paths"] = np.array(list(ds.keys()))
+    for k, v in ds.items():
+        out["ds:" + k] = v
+    rng = np.random.default_rng(5)
+    for (a, b) in ((6, 6), (5, 5), (4, 6)):
+        m2 = ref.RefMeasure(a, b)
+        c = rng.standard_normal((3, a * b, a * b))
+        r = m2.chi_site_to_chi_r(c)
+        out[f"tf_{a}x{b}_site"] = c
+        out[f"tf_{a}x{b}_r"] = r
+        if a == b:
+            k = m2.chi_r_to_chi_k(r)
+            out[f"tf_{a}x{b}_k"] = k
+        m2.close()
+    out["pbc_shortest_L4567"] = np.array([[mm.pbc_shortest(d, L) if abs(d) < L else 0 for d in range(-6, 7)] for L in (4, 5, 6, 7)])
+    mm.close()
+    np.savez_compressed(os.path.join(HERE, "measure.npz"), **out)
+
+
 if __name__ == "__main__":
     assert ref.build(), "oracle/_ref could not be built (needs /root/reference)"
     for nm, cfg in CASES.items():
@@ -182,4 +222,5 @@ if __name__ == "__main__":
     stablelinalg_case()
     misc_case()
     exchange_case()
+    measure_case()
     print("golden fixtures written to", HERE)

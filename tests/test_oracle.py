@@ -262,3 +262,46 @@ def test_live_reference_stablelinalg():
     Gr, ldr = ref.inv_I_plus_ldr((Lr, dr, Rr))
     Go, ldo = O.inv_I_plus_ldr(O.LDR(Lr, dr, Rr))
     assert rel(Go, Gr) < TOL and abs(ldo - ldr) < 1e-10 * max(1, abs(ldr))
+
+
+# ---- measurement pipeline (include/measurementh5.h), SURVEY.md 8f rank 1 ------------------------------
+def test_measurement_manager_golden():
+    """The oracle's MeasurementManager reproduces every dataset the reference's would have written
+    (same paths, dims and values) for 2 bins x 4 measurements of a real 6x6 trajectory."""
+    g = load("measure.npz")
+    mm = O.MeasurementManager(6, 6)
+    for b in range(2):
+        for k in range(4):
+            mm.measure(g["G"][4 * b + k])
+        mm.accumulate()
+    paths = [str(p) for p in g["paths"]]
+    assert sorted(paths) == sorted(mm.datasets)
+    assert str(g["file_name"]) == "results/data_2.h5"
+    for p in paths:
+        want = g["ds:" + p]
+        assert mm.datasets[p].shape == want.shape, p
+        assert rel(mm.datasets[p], want) < TOL, p
+    assert g["ds:/bin_0/equaltime/densityCorr"].shape == (6, 6, 1)
+    assert g["ds:/binK_0/equaltime/densityCorr"].shape == (6, 6, 1, 2)
+
+
+def test_measurement_transforms_golden():
+    g = load("measure.npz")
+    for (a, b) in ((6, 6), (5, 5), (4, 6)):
+        r = O.chi_site_to_chi_r(g[f"tf_{a}x{b}_site"], a, b)
+        assert r.shape == (a, b, 3) and rel(r, g[f"tf_{a}x{b}_r"]) < 1e-13
+        if a == b:
+            k, want = O.chi_r_to_chi_k(r, a, b), g[f"tf_{a}x{b}_k"]
+            assert rel(np.stack([k.real, k.imag]), np.stack([want.real, want.imag])) < 1e-13
+    tab = g["pbc_shortest_L4567"]
+    for li, L in enumerate((4, 5, 6, 7)):
+        for di, d in enumerate(range(-6, 7)):
+            if abs(d) < L:
+                assert O.pbc_shortest(d, L) == tab[li, di]
+    # the fold conserves the sum of all pair entries (each pair lands in exactly one bin, / n_cells)
+    c = g["tf_4x6_site"]
+    assert np.allclose(O.chi_site_to_chi_r(c, 4, 6).sum(axis=(0, 1)), c.sum(axis=(1, 2)) / 24)
+    # k = 0 component of the transform is the plain sum over displacements
+    r = g["tf_6x6_r"]
+    k = O.chi_r_to_chi_k(r, 6, 6)
+    assert np.allclose(k[6 // 2 - 1, 6 // 2 - 1, :], r.sum(axis=(0, 1)))

@@ -12,6 +12,7 @@
 #else
 #include <algorithm>
 #include <cmath>
+#include <complex>
 #include <cstddef>
 #include <cstring>
 #include <initializer_list>
@@ -76,10 +77,39 @@ class Col : public Mat<T> {
     using Mat<T>::zeros;
 };
 
+// (n_rows, n_cols, n_slices), column-major with slices consecutive -- arma::Cube's memory order
+template <typename T>
+class Cube {
+   public:
+    uword n_rows = 0, n_cols = 0, n_slices = 0, n_elem = 0;
+    Cube() = default;
+    Cube(uword r, uword c, uword s) { set_size(r, c, s); }
+    void set_size(uword r, uword c, uword s) {
+        n_rows = r;
+        n_cols = c;
+        n_slices = s;
+        n_elem = r * c * s;
+        data_.assign(n_elem, T());
+    }
+    void zeros() { std::fill(data_.begin(), data_.end(), T()); }
+    T* memptr() { return data_.data(); }
+    const T* memptr() const { return data_.data(); }
+    T* slice_memptr(uword s) { return data_.data() + s * n_rows * n_cols; }
+    const T* slice_memptr(uword s) const { return data_.data() + s * n_rows * n_cols; }
+    T& operator()(uword i, uword j, uword k) { return data_[i + n_rows * (j + n_cols * k)]; }
+    const T& operator()(uword i, uword j, uword k) const { return data_[i + n_rows * (j + n_cols * k)]; }
+
+   private:
+    std::vector<T> data_;
+};
+
 typedef Mat<double> mat;
 typedef Col<double> vec;
 typedef Mat<long long> imat;  // arma::imat is 64-bit
 typedef Col<uword> uvec;
+typedef std::complex<double> cx_double;
+typedef Cube<double> cube;
+typedef Cube<cx_double> cx_cube;
 
 }  // namespace arma
 #endif  // DQMCB_USE_ARMADILLO

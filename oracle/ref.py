@@ -24,11 +24,11 @@ _llp = C.POINTER(C.c_longlong)
 
 def build(reference_root: str = "/root/reference", force: bool = False) -> bool:
     """Compile oracle/_ref when the reference tree is present (this container only)."""
-    if os.path.exists(LIB_PATH) and not force:
-        return True
-    if not os.path.isdir(reference_root):
-        return False
-    subprocess.check_call(["make", "-C", _HERE, f"REF={reference_root}"], stdout=subprocess.DEVNULL)
+    if not os.path.isdir(reference_root):  # GPU box: the prebuilt .so travels with the snapshot
+        return os.path.exists(LIB_PATH)
+    if force:
+        subprocess.check_call(["make", "-C", _HERE, "clean"], stdout=subprocess.DEVNULL)
+    subprocess.check_call(["make", "-C", _HERE, f"REF={reference_root}"], stdout=subprocess.DEVNULL)  # incremental
     return os.path.exists(LIB_PATH)
 
 

@@ -7,6 +7,7 @@
 //   host_mirror_test traj  L1 L2 U t mu beta nt n_stab seed n_sweeps out.txt
 //   host_mirror_test exchange out.txt         (4-replica beta ladder of tests/golden/exchange.npz)
 //   host_mirror_test api out.txt              (stablelinalg / containers / error behaviour)
+//   host_mirror_test measure in.txt out.txt   (MeasurementManager / transform:: on the G's of tests/golden/measure.npz)
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -17,6 +18,7 @@
 #include <dqmcb/dqmc.h>
 #include <dqmcb/field.h>
 #include <dqmcb/lattice.h>
+#include <dqmcb/measurementh5.h>
 #include <dqmcb/model.h>
 #include <dqmcb/stablelinalg.h>
 #include <dqmcb/stackngf.h>
@@ -212,12 +214,100 @@ static int run_api(int argc, char** argv) {
     return 0;
 }
 
+// MeasurementManager wired as source/main.cpp:114-119,165-170, on Green's functions read from a file
+// ("n_mats n_sites" then the matrices, column-major): (A) the reference-style host path through
+// registered calculators, (B) the batched device path.  2 bins x n_mats/2 measurements each.
+static int run_measure(int argc, char** argv) {
+    if (argc < 4) return 2;
+    FILE* in = fopen(argv[2], "r");
+    FILE* f = fopen(argv[3], "w");
+    if (!in || !f) return 3;
+    int n_mats = 0, n = 0;
+    if (fscanf(in, "%d %d", &n_mats, &n) != 2) return 3;
+    std::vector<arma::mat> Gs(n_mats);
+    for (auto& G : Gs) {
+        G.set_size(n, n);
+        for (int e = 0; e < n * n; ++e)
+            if (fscanf(in, "%lf", G.memptr() + e) != 1) return 3;
+    }
+    fclose(in);
+    int L = 1;
+    while (L * L < n) ++L;
+    utility::parameters params = make_params(L, L, 4.0, 1.0, -0.1, 2.0, 20, 5);
+    utility::random rng(1);
+    Lattice lat(params, {1.0, 0.0}, {0.0, 1.0}, {{0.0, 0.0}});
+    AttractiveHubbard model(params, lat, rng, 2.0);
+    DQMC sim(params, model);
+    std::vector<LDRStack> stacks(1);
+    std::vector<GF> greens(1);
+    stacks[0] = sim.init_stacks(0);
+    greens[0] = sim.init_greenfunctions(stacks[0]);
+
+    MeasurementManager host_mm(params, 0, 2), dev_mm(params, 0, 2);
+    host_mm.addScalar("density", [&](const std::vector<GF>& g, const Lattice& l) { return Observables::calculate_density(model, g, l); });
+    host_mm.addScalar("doubleOcc", [&](const std::vector<GF>& g, const Lattice& l) { return Observables::calculate_doubleOccupancy(model, g, l); });
+    host_mm.addScalar("swave", [&](const std::vector<GF>& g, const Lattice& l) { return Observables::calculate_swavePairing(model, g, l); });
+    host_mm.addEqualTime("densityCorr", [&](const std::vector<GF>& g, const Lattice& l) { return Observables::calculate_densityCorr(model, g, l); });
+    const int per_bin = n_mats / 2;
+    for (int b = 0; b < 2; ++b) {
+        for (int k = 0; k < per_bin; ++k) {
+            greens[0].Gtt[0] = Gs[b * per_bin + k];
+            host_mm.measure(greens, lat);
+            model.upload_G(greens[0].Gtt[0]);
+            dev_mm.measure_device(model, lat);
+        }
+        host_mm.accumulate(lat);
+        dev_mm.accumulate(lat);
+    }
+    for (const auto* mm : {&host_mm, &dev_mm}) {
+        const std::string tag = (mm == &host_mm) ? "A:" : "B:";
+        for (const auto& d : mm->store().datasets()) {
+            dump(f, tag + d.path, d.data.data(), d.data.size());
+            std::vector<double> dims(d.dims.begin(), d.dims.end());
+            dump(f, tag + "dims:" + d.path, dims.data(), dims.size());
+        }
+    }
+    // stand-alone transforms on a 2-slice cube built from the first two matrices
+    arma::cube c(n, n, 2);
+    for (int s2 = 0; s2 < 2; ++s2) std::copy(Gs[s2].memptr(), Gs[s2].memptr() + n * n, c.slice_memptr(s2));
+    const arma::cube r = transform::chi_site_to_chi_r(c, lat);
+    const arma::cx_cube k = transform::chi_r_to_chi_k(r, lat);
+    dump(f, "tf_r", r.memptr(), r.n_elem);
+    dump(f, "tf_k", reinterpret_cast<const double*>(k.memptr()), 2 * k.n_elem);
+    double meta[3] = {(double)host_mm.current_bin(), (double)transform::pbc_shortest(4, 6), (double)transform::pbc_shortest(-3, 6)};
+    dump(f, "meta", meta, 3);
+    int threw = 0;
+    try {
+        utility::parameters p2 = make_params(L, L, 4.0, 1.0, -0.1, 2.0, 20, 5);
+        p2.set("simulation", "isMeasureUnequalTime", "true");
+        MeasurementManager m3(p2, 0, 0);
+        m3.addUnequalTime("greenTau", [](const std::vector<GF>&, const Lattice&) { return arma::cube(); });
+    } catch (const std::runtime_error&) {
+        threw = 1;
+    }
+    double th = threw;
+    dump(f, "unequal_throws", &th, 1);
+#ifdef DQMCB_USE_HDF5
+    // built against the HDF5 recorder shim (oracle/shim/hdf5.h): what the HDF5 branch of the mirror wrote
+    for (const auto& d : h5shim::store().sets) {
+        dump(f, "H:" + d.path, d.data.data(), d.data.size());
+        std::vector<double> dims(d.dims.begin(), d.dims.end());
+        dump(f, "H:dims:" + d.path, dims.data(), dims.size());
+    }
+    double nfiles = (double)h5shim::store().files.size();
+    dump(f, "H:n_files", &nfiles, 1);
+#endif
+    fclose(f);
+    return 0;
+}
+
 int main(int argc, char** argv) {
     if (argc < 2) return 2;
     try {
         if (!strcmp(argv[1], "traj")) return run_traj(argc, argv);
         if (!strcmp(argv[1], "exchange")) return run_exchange(argc, argv);
         if (!strcmp(argv[1], "api")) return run_api(argc, argv);
+        if (!strcmp(argv[1], "measure")) return run_measure(argc, argv);
     } catch (const std::exception& e) {
         fprintf(stderr, "host_mirror_test: %s\n", e.what());
         return 1;

@@ -120,3 +120,43 @@ def test_stablelinalg_and_containers(tmp_path):
     assert rel(cm(o["inv_invldr_plus_ldr"]), O.inv_invldr_plus_ldr(F, F2)) < 1e-10
     assert list(o["exceptions"]) == [1, 1, 1, 1]
     assert [int(x) for x in o["partner_rank_ws8_a1"]] == [O.partner_rank(r, 8, 1) for r in range(8)]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("variant", ["", "_h5"])
+def test_measurement_manager_mirror(variant, tmp_path):
+    """MeasurementManager / transform:: of include/dqmcb/measurementh5.h on the G's of the reference run
+    behind tests/golden/measure.npz: the reference-style host path (A), the batched device path (B) and
+    -- for the _h5 build, compiled with the mirror's HDF5 branch over the HDF5 recorder shim -- the
+    datasets the HDF5 calls carried (H) all equal what the reference wrote."""
+    from oracle import dqmc_oracle as O
+
+    g = np.load(os.path.join(GOLD, "measure.npz"))
+    inp = tmp_path / "g.txt"
+    with open(inp, "w") as f:
+        f.write(f"{g['G'].shape[0]} 36\n")
+        for G in g["G"]:
+            f.write(" ".join(repr(float(x)) for x in G.ravel(order="F")) + "\n")
+    out = str(tmp_path / "out.txt")
+    r = subprocess.run([BIN + variant, "measure", str(inp), out], capture_output=True, text=True, timeout=600, cwd=str(tmp_path))
+    assert r.returncode == 0, r.stderr
+    o = parse(out)
+    paths = [str(p) for p in g["paths"]]
+    for tag in ("A:", "B:") + (("H:",) if variant else ()):
+        got_paths = [k[len(tag):] for k in o if k.startswith(tag) and not k.startswith(tag + "dims:") and k != "H:n_files"]
+        assert sorted(got_paths) == sorted(paths), tag
+        for p in paths:
+            want = g["ds:" + p]
+            assert [int(x) for x in o[tag + "dims:" + p]] == list(want.shape), (tag, p)
+            assert rel(o[tag + p].reshape(want.shape), want) < 1e-10, (tag, p)
+    if variant:
+        assert o["H:n_files"][0] == 2  # one results/data_<rank>.h5 per manager
+    # stand-alone transforms on a 2-slice cube of the first two G's
+    c = g["G"][:2]
+    want_r = O.chi_site_to_chi_r(c, 6, 6)
+    assert rel(o["tf_r"].reshape((6, 6, 2), order="F"), want_r) < 1e-12
+    want_k = O.chi_r_to_chi_k(want_r, 6, 6)
+    z = o["tf_k"][0::2] + 1j * o["tf_k"][1::2]
+    assert np.max(np.abs(z.reshape((6, 6, 2), order="F") - want_k)) < 1e-12 * np.max(np.abs(want_k))
+    assert list(o["meta"]) == [2, O.pbc_shortest(4, 6), O.pbc_shortest(-3, 6)]
+    assert o["unequal_throws"][0] == 1

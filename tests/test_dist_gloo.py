@@ -157,3 +157,65 @@ def test_replica_exchange_world2_gloo():
             assert np.array_equal(fields[r, w], sims[r].m.fields), f"ladder {w} rank {r}"
     assert attempt == 2 and accepted == int(accs.sum())
     assert np.allclose(red, [1.5, 3.0])  # mean over 4 walkers of (1,2),(1,2),(2,4),(2,4)
+
+
+# ---- pooled measurement bins over ranks (dqmc_b200/measure.py) -----------------------------------------
+class _FakeBinCtx:
+    """Stands in for capi.Context's bin_* calls (which need a GPU): rank-dependent sums and counts."""
+
+    def __init__(self, rank):
+        self.N, self.rank = 16, rank
+        self.calls = 0
+
+    def bin_configure(self, L1, L2):
+        pass
+
+    def bin_measure(self):
+        self.calls += 1
+
+    def bin_fetch(self, reset=True):
+        n = 10 * (self.rank + 1) * self.calls
+        sc = np.array([1.0, 2.0, 3.0]) * n * (self.rank + 1)
+        chi = np.arange(16, dtype=np.float64).reshape((4, 4), order="F") * n * (self.rank + 2)
+        self.calls = 0
+        return sc, chi, n
+
+
+def _bin_worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from dqmc_b200 import capi, measure
+
+        # the Fourier transform of a bin is a device call; no GPU here, so the test substitutes the oracle's
+        capi.chi_r_to_chi_k = lambda r, L1, L2, device=0: O.chi_r_to_chi_k(r, L1, L2)
+        mm = measure.MeasurementManager(_FakeBinCtx(rank), 4, 4, rank=rank, pool_ranks=True)
+        mm.measure()
+        mm.measure()
+        new = mm.accumulate()
+        if rank == 0:
+            out.put({k: v for k, v in new.items()})
+    finally:
+        dist.destroy_process_group()
+
+
+def test_pooled_measurement_bin_world2_gloo():
+    world = 2
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_bin_worker, args=(r, world, port, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    new = out.get(timeout=300)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    # rank 0: n=20, sc = (1,2,3)*20 ; rank 1: n=40, sc = (1,2,3)*80 -> pooled mean (1,2,3)*100/60
+    assert np.allclose([new[f"/bin_0/scalar/{k}"][0] for k in ("density", "doubleOcc", "swave")], np.array([1, 2, 3]) * 100 / 60)
+    base = np.arange(16, dtype=np.float64).reshape((4, 4), order="F")
+    want = base * (20 * 2 + 40 * 3) / 60
+    assert np.allclose(new["/bin_0/equaltime/densityCorr"][:, :, 0], want)
+    k = O.chi_r_to_chi_k(want[:, :, None], 4, 4)
+    assert np.allclose(new["/binK_0/equaltime/densityCorr"][..., 0], k.real) and new["/binK_0/equaltime/densityCorr"].shape == (4, 4, 1, 2)

@@ -52,7 +52,8 @@ SYMBOLS = [
     "dqmcb_timing_enable", "dqmcb_timing_get", "dqmcb_inv_invldr_plus_ldr", "dqmcb_local_update_ratio",
     "dqmcb_update_greens_local", "dqmcb_set_single_field", "dqmcb_launch_count", "dqmcb_n_groups",
     "dqmcb_bin_configure", "dqmcb_bin_measure", "dqmcb_bin_fetch", "dqmcb_chi_site_to_chi_r", "dqmcb_chi_r_to_chi_k",
-    "dqmcb_pbc_shortest",
+    "dqmcb_pbc_shortest", "dqmcb_sweep_unequal_time", "dqmcb_get_G_unequal", "dqmcb_get_unequal_err",
+    "dqmcb_half_wrap_unequal", "dqmcb_measure_unequal_time", "dqmcb_bin_measure_unequal", "dqmcb_bin_fetch_unequal",
 ]
 
 
@@ -92,6 +93,13 @@ def lib():
         L.dqmcb_chi_site_to_chi_r.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, _dp, _dp]
         L.dqmcb_chi_r_to_chi_k.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, _dp, _dp]
         L.dqmcb_pbc_shortest.argtypes = [C.c_int, C.c_int]
+        L.dqmcb_sweep_unequal_time.argtypes = [C.c_void_p]
+        L.dqmcb_get_G_unequal.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp]
+        L.dqmcb_get_unequal_err.argtypes = [C.c_void_p, _dp]
+        L.dqmcb_half_wrap_unequal.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp]
+        L.dqmcb_measure_unequal_time.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp, _dp, _dp]
+        L.dqmcb_bin_measure_unequal.argtypes = [C.c_void_p]
+        L.dqmcb_bin_fetch_unequal.argtypes = [C.c_void_p, _dp, C.POINTER(C.c_longlong), C.c_int]
         for name in ("dqmcb_synchronize", "dqmcb_init_stacks", "dqmcb_init_greenfunctions", "dqmcb_sweep_0_to_beta",
                      "dqmcb_sweep_beta_to_0", "dqmcb_reset_stats", "dqmcb_n_stack"):
             getattr(L, name).argtypes = [C.c_void_p]
@@ -297,6 +305,43 @@ class Context:
         n = C.c_longlong(0)
         self._ck(self.L.dqmcb_bin_fetch(self.h, _d(sc), _d(chi), C.byref(n), int(bool(reset))))
         return sc, chi.reshape((L1, L2), order="F"), int(n.value)
+
+    # --- unequal time (source/dqmc.cpp:223-280,458-514) ---
+    def sweep_unequal_time(self) -> None:
+        self._ck(self.L.dqmcb_sweep_unequal_time(self.h))
+
+    def get_G_unequal(self, which: int, l: int) -> np.ndarray:
+        """which: 0 Gtt[l], 1 Gt0[l], 2 G0t[l] -> [W, N, N]."""
+        out = np.empty((self.W, self.N, self.N))
+        self._ck(self.L.dqmcb_get_G_unequal(self.h, which, l, _d(out)))
+        return _from_cm(out)
+
+    def get_unequal_err(self) -> np.ndarray:
+        e = np.empty(self.W)
+        self._ck(self.L.dqmcb_get_unequal_err(self.h, _d(e)))
+        return e
+
+    def half_wrap_unequal(self, which: int, l: int) -> np.ndarray:
+        out = np.empty((self.W, self.N, self.N))
+        self._ck(self.L.dqmcb_half_wrap_unequal(self.h, which, l, _d(out)))
+        return _from_cm(out)
+
+    def measure_unequal_time(self, L1: int, L2: int):
+        """greenTau, doublonTau, currxxTau: [W, nt+1, N, N] each."""
+        outs = [np.empty((self.W, self.nt + 1, self.N, self.N)) for _ in range(3)]
+        self._ck(self.L.dqmcb_measure_unequal_time(self.h, L1, L2, *[_d(o) for o in outs]))
+        return tuple(_from_cm(o) for o in outs)
+
+    def bin_measure_unequal(self) -> None:
+        self._ck(self.L.dqmcb_bin_measure_unequal(self.h))
+
+    def bin_fetch_unequal(self, reset=True):
+        """(chi_r_sums[3, L1, L2, nt+1] for greenTau/doublonTau/currxxTau, n_samples)."""
+        L1, L2 = self._bin_shape
+        buf = np.empty((3, self.nt + 1, L2, L1))
+        n = C.c_longlong(0)
+        self._ck(self.L.dqmcb_bin_fetch_unequal(self.h, _d(buf), C.byref(n), int(bool(reset))))
+        return np.ascontiguousarray(buf.transpose(0, 3, 2, 1)), int(n.value)
 
     def global_action(self) -> np.ndarray:
         S = np.empty(self.W)

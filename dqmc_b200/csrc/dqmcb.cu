@@ -107,6 +107,7 @@ __device__ inline double* stkD(const Params& p, int w, int i) { return p.stackD 
 __device__ inline void store_d(double* dst, const double* src, int n) {
     for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
 }
+#include "unequal.cuh"  // needs the stack accessors above
 
 // End-of-block work of the sweeps (source/dqmc.cpp:369-394 forward, 429-454 backward):
 // Bbar from the current fields, stack update, stabilised G, check_error against the wrapped G.
@@ -604,6 +605,7 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
     CKC(cudaFuncSetAttribute(k_init_stacks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
     CKC(cudaFuncSetAttribute(k_init_green, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
     CKC(cudaFuncSetAttribute(k_ldr_op, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
+    CKC(cudaFuncSetAttribute(k_uneq_block, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
     { const char* fg = getenv("DQMCB_FORCE_GENERIC"); ctx->force_generic = fg && fg[0] == (char)49; }
     {
         const char* pp = getenv("DQMCB_PHASE_PROF");
@@ -657,6 +659,11 @@ void dqmcb_destroy(dqmcb_ctx* ctx) {
     cudaFree(ctx->d_obs);
     cudaFree(ctx->d_binpart);
     cudaFree(ctx->d_binacc);
+    cudaFree(ctx->d_uneq);
+    cudaFree(ctx->d_bt0);
+    cudaFree(ctx->d_uneq_err);
+    cudaFree(ctx->d_tbinpart);
+    cudaFree(ctx->d_tbinacc);
     cudaFree(ctx->d_scratchNN);
     cudaFree(ctx->d_tape_perm);
     cudaFree(ctx->d_tape_k);
@@ -1193,6 +1200,140 @@ int dqmcb_chi_r_to_chi_k(int device, int L1, int L2, int n_mats, const double* c
     return run_transform(device, L1, L2, n_mats, chi_r, n, chi_k, 2 * n, 1);
 }
 int dqmcb_pbc_shortest(int d, int L) { return dq::pbc_shortest(d, L); }
+
+// ---- unequal-time sweep (source/dqmc.cpp:223-280,458-514) ---------------------------------------------
+static UneqBufs uneq_bufs(dqmcb_ctx* ctx) { return UneqBufs{ctx->d_uneq, ctx->d_bt0, ctx->d_uneq_err}; }
+
+int dqmcb_sweep_unequal_time(dqmcb_ctx* ctx) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    if (!ctx->stacks_ready || !ctx->green_ready) {
+        ctx->err = "dqmcb_sweep_unequal_time: needs the state after sweep_beta_to_0 (stack + G(0,0))";
+        return DQMCB_ESTATE;
+    }
+    const size_t nn = (size_t)p.N * p.N;
+    if (!ctx->d_uneq) {
+        CK(cudaMalloc(&ctx->d_uneq, (size_t)p.W * 3 * (p.nt + 1) * nn * 8));
+        CK(cudaMalloc(&ctx->d_bt0, (size_t)p.W * (2 * nn + p.N) * 8));
+        CK(cudaMalloc(&ctx->d_uneq_err, (size_t)p.W * 8));
+    }
+    for (int i = 0; i < p.n_stack; ++i) {
+        TimeScope ts(ctx, DQMCB_K_OTHER);
+        k_uneq_block<<<p.W, kThreads, ctx->smem_stab, ctx->stream>>>(p, uneq_bufs(ctx), i);
+        ctx->n_launches += 1;
+    }
+    CK(cudaGetLastError());
+    ctx->uneq_ready = true;
+    return DQMCB_OK;
+}
+#define NEED_UNEQ(ctx)                                                              \
+    if (!(ctx)->uneq_ready) {                                                       \
+        (ctx)->err = "unequal-time data missing: call dqmcb_sweep_unequal_time first"; \
+        return DQMCB_ESTATE;                                                        \
+    }
+int dqmcb_get_G_unequal(dqmcb_ctx* ctx, int which, int l, double* out) {
+    NEED(ctx);
+    NEED_UNEQ(ctx);
+    const Params& p = ctx->p;
+    if (which < 0 || which > 2 || l < 0 || l > p.nt || !out) {
+        ctx->err = "dqmcb_get_G_unequal: which in 0..2, l in 0..nt";
+        return DQMCB_EINVAL;
+    }
+    const size_t nn = (size_t)p.N * p.N;
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy2D(out, nn * 8, ctx->d_uneq + ((size_t)which * (p.nt + 1) + l) * nn, (size_t)3 * (p.nt + 1) * nn * 8, nn * 8, p.W,
+                    cudaMemcpyDeviceToHost));
+    return DQMCB_OK;
+}
+int dqmcb_get_unequal_err(dqmcb_ctx* ctx, double* err_max) {
+    NEED(ctx);
+    NEED_UNEQ(ctx);
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(err_max, ctx->d_uneq_err, (size_t)ctx->p.W * 8, cudaMemcpyDeviceToHost));
+    return DQMCB_OK;
+}
+int dqmcb_half_wrap_unequal(dqmcb_ctx* ctx, int which, int l, double* Gsym) {
+    NEED(ctx);
+    NEED_UNEQ(ctx);
+    const Params& p = ctx->p;
+    if (which < 0 || which > 2 || l < 0 || l > p.nt || !Gsym) {
+        ctx->err = "dqmcb_half_wrap_unequal: which in 0..2, l in 0..nt";
+        return DQMCB_EINVAL;
+    }
+    k_uneq_half_wrap<<<p.W, kThreads, 0, ctx->stream>>>(p, uneq_bufs(ctx), which, l, ctx->d_scratchNN);
+    ctx->n_launches += 1;
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(Gsym, ctx->d_scratchNN, (size_t)p.W * p.N * p.N * 8, cudaMemcpyDeviceToHost));
+    return DQMCB_OK;
+}
+int dqmcb_measure_unequal_time(dqmcb_ctx* ctx, int L1, int L2, double* green, double* doublon, double* currxx) {
+    NEED(ctx);
+    NEED_UNEQ(ctx);
+    const Params& p = ctx->p;
+    if (L1 <= 0 || L2 <= 0 || L1 * L2 != p.N) {
+        ctx->err = "dqmcb_measure_unequal_time: L1*L2 must equal n_sites";
+        return DQMCB_EINVAL;
+    }
+    const size_t per = (size_t)p.W * (p.nt + 1) * p.N * p.N;
+    double* outs[3] = {green, doublon, currxx};
+    double* d[3] = {nullptr, nullptr, nullptr};
+    int rc = DQMCB_OK;
+    for (int k = 0; k < 3 && rc == DQMCB_OK; ++k)
+        if (outs[k] && cudaMalloc(&d[k], per * 8) != cudaSuccess) rc = DQMCB_ECUDA;
+    if (rc == DQMCB_OK) {
+        k_uneq_obs_site<<<dim3(p.nt + 1, p.W), kThreads, 0, ctx->stream>>>(p, uneq_bufs(ctx), L1, d[0], d[1], d[2]);
+        ctx->n_launches += 1;
+        if (cudaGetLastError() != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess) rc = DQMCB_ECUDA;
+    }
+    for (int k = 0; k < 3; ++k) {
+        if (rc == DQMCB_OK && outs[k] && cudaMemcpy(outs[k], d[k], per * 8, cudaMemcpyDeviceToHost) != cudaSuccess) rc = DQMCB_ECUDA;
+        cudaFree(d[k]);
+    }
+    if (rc != DQMCB_OK) ctx->err = "dqmcb_measure_unequal_time: CUDA failure";
+    return rc;
+}
+// MeasurementManager::measure for the three unequal-time observables of source/main.cpp:120-122, all walkers,
+// folded onto displacements and accumulated on the device (needs dqmcb_bin_configure for L1, L2)
+int dqmcb_bin_measure_unequal(dqmcb_ctx* ctx) {
+    NEED(ctx);
+    NEED_UNEQ(ctx);
+    const Params& p = ctx->p;
+    if (!ctx->d_binacc) {
+        ctx->err = "dqmcb_bin_measure_unequal: call dqmcb_bin_configure first";
+        return DQMCB_ESTATE;
+    }
+    const int len = 3 * (p.nt + 1) * p.N;
+    if (!ctx->d_tbinpart) {
+        CK(cudaMalloc(&ctx->d_tbinpart, (size_t)p.W * len * 8));
+        CK(cudaMalloc(&ctx->d_tbinacc, (size_t)len * 8));
+        CK(cudaMemsetAsync(ctx->d_tbinacc, 0, (size_t)len * 8, ctx->stream));
+        ctx->tbin_samples = 0;
+    }
+    k_uneq_bin<<<dim3(p.nt + 1, p.W), 128, 0, ctx->stream>>>(p, uneq_bufs(ctx), ctx->bin_L1, ctx->bin_L2, ctx->d_tbinpart);
+    k_bin_reduce<<<(len + 127) / 128, 128, 0, ctx->stream>>>(p.W, len, ctx->d_tbinpart, ctx->d_tbinacc);
+    ctx->n_launches += 2;
+    CK(cudaGetLastError());
+    ctx->tbin_samples += p.W;
+    return DQMCB_OK;
+}
+int dqmcb_bin_fetch_unequal(dqmcb_ctx* ctx, double* chi_r_sums, long long* n_samples, int reset) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    if (!ctx->d_tbinacc) {
+        ctx->err = "dqmcb_bin_fetch_unequal: nothing measured";
+        return DQMCB_ESTATE;
+    }
+    const size_t len = (size_t)3 * (p.nt + 1) * p.N;
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (chi_r_sums) CK(cudaMemcpy(chi_r_sums, ctx->d_tbinacc, len * 8, cudaMemcpyDeviceToHost));
+    if (n_samples) *n_samples = ctx->tbin_samples;
+    if (reset) {
+        CK(cudaMemsetAsync(ctx->d_tbinacc, 0, len * 8, ctx->stream));
+        ctx->tbin_samples = 0;
+    }
+    return DQMCB_OK;
+}
 
 int dqmcb_global_action(dqmcb_ctx* ctx, double* S) {
     NEED(ctx);

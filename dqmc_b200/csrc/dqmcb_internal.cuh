@@ -84,6 +84,11 @@ struct dqmcb_ctx {
     double* d_binpart = nullptr;    // [W][3 + N]
     double* d_binacc = nullptr;     // [3 + N]
     long long bin_samples = 0;
+    // unequal-time sweep (dqmcb_sweep_unequal_time): Gtt/Gt0/G0t for every slice, running left product, error
+    double *d_uneq = nullptr, *d_bt0 = nullptr, *d_uneq_err = nullptr;
+    bool uneq_ready = false;
+    double *d_tbinpart = nullptr, *d_tbinacc = nullptr;  // [W][3][nt+1][N], [3][nt+1][N]
+    long long tbin_samples = 0;
     size_t smem_prop = 0, smem_stab = 0;
     // optional per-launch timing
     // walker groups: independent chains split over `n_groups` streams so that the partial last wave of

@@ -148,6 +148,27 @@ int dqmcb_chi_r_to_chi_k(int device, int L1, int L2, int n_mats, const double* c
 /* transform::pbc_shortest (include/measurementh5.h:13-17); host arithmetic, needs no device */
 int dqmcb_pbc_shortest(int d, int L);
 
+/* ---- unequal-time sweep -----------------------------------------------------------
+ * DQMC::sweep_unequalTime (source/dqmc.cpp:458-514: propagate_unequalTime_GF_forward :223-246,
+ * propagate_Bt0_Bbt :248-262, stabilize_unequalTime :264-280) for every walker.  Call after
+ * dqmcb_sweep_beta_to_0 (needs G(0,0) and the right-product stack); fills G(tau,tau), G(tau,0), G(0,tau)
+ * for tau = 0..nt on the device, leaves the stack untouched and updates logdet at tau = beta. */
+int dqmcb_sweep_unequal_time(dqmcb_ctx* ctx);
+/* which: 0 Gtt[l], 1 Gt0[l], 2 G0t[l] (include/stackngf.h:15-22), l in 0..nt: out[W][N*N] column-major */
+int dqmcb_get_G_unequal(dqmcb_ctx* ctx, int which, int l, double* out);
+/* largest check_error of the sweep's stabilisations per walker (the reference warns above 1e-6, :505-508) */
+int dqmcb_get_unequal_err(dqmcb_ctx* ctx, double* err_max);
+/* DQMC::half_warp for the unequal-time arrays (source/dqmc.cpp:303-312): invexpKhalf X[which][l] expKhalf */
+int dqmcb_half_wrap_unequal(dqmcb_ctx* ctx, int which, int l, double* Gsym);
+/* Observables::calculate_{greenTau,doublonTau,currxxTau} (source/model.cpp:290-392), site-indexed:
+ * each out[W][nt+1][N*N] column-major slices of the reference's cube; any may be NULL */
+int dqmcb_measure_unequal_time(dqmcb_ctx* ctx, int L1, int L2, double* green, double* doublon, double* currxx);
+/* the same three observables for all walkers, folded onto displacements and accumulated on the device
+ * (MeasurementManager::measure for source/main.cpp:120-122); needs dqmcb_bin_configure.
+ * fetch: chi_r_sums[3][nt+1][L1*L2] (greenTau, doublonTau, currxxTau; element (bx,by) at bx + L1*by), SUMS */
+int dqmcb_bin_measure_unequal(dqmcb_ctx* ctx);
+int dqmcb_bin_fetch_unequal(dqmcb_ctx* ctx, double* chi_r_sums, long long* n_samples, int reset);
+
 /* AttractiveHubbard::global_action, source/model.cpp:140-159: S[W] */
 int dqmcb_global_action(dqmcb_ctx* ctx, double* S);
 /* DQMC::half_warp, equal-time entry (source/dqmc.cpp:288-315): Gsym[W][N*N] = invexpKhalf G expKhalf */

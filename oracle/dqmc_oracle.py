@@ -450,6 +450,48 @@ class DQMC:
     def mean_err(self) -> float:
         return self.total_err / self.n_err if self.n_err else float("nan")
 
+    # --- unequal time (source/dqmc.cpp:223-280, 458-514) ---
+    def sweep_unequalTime(self) -> float:
+        """After sweep_beta_to_0 (self.G = Gtt[0], stack = right products B(beta, tau)): fills
+        self.Gtt_all / Gt0_all / G0t_all [nt+1, N, N]; returns the largest stabilisation error seen."""
+        n, nt = self.m.ns, self.nt
+        Gtt = np.zeros((nt + 1, n, n))
+        Gt0 = np.zeros((nt + 1, n, n))
+        G0t = np.zeros((nt + 1, n, n))
+        Gtt[0] = self.G
+        Bt0 = None
+        worst = 0.0
+        for l in range(nt):
+            i_stack, loc_l = l // self.n_stab, l % self.n_stab
+            if l == 0:  # :235-240
+                Gt0[0] = Gtt[0]
+                G0t[0] = Gtt[0] - np.eye(n)
+            B, iB = self.B(l), self.invB(l)
+            Gtt[l + 1] = B @ Gtt[l] @ iB  # :241-243
+            Gt0[l + 1] = B @ Gt0[l]
+            G0t[l + 1] = G0t[l] @ iB
+            if loc_l == self.loc_l_end[i_stack]:
+                tmp = (Gtt[l + 1].copy(), Gt0[l + 1].copy(), G0t[l + 1].copy())
+                Bbar = self.calculate_Bbar(i_stack)
+                Bt0 = to_LDR(Bbar) if i_stack == 0 else mat_mul_ldr(Bbar, Bt0)  # propagate_Bt0_Bbt :248-262
+                if l == nt - 1:  # stabilize_unequalTime :264-280
+                    Gtt[l + 1], self.log_det_M = inv_I_plus_ldr(Bt0)
+                    Gt0[l + 1] = np.eye(n) - Gtt[l + 1]
+                    G0t[l + 1] = -Gtt[l + 1]
+                else:
+                    Bbt = self.stack[i_stack + 1]
+                    Gtt[l + 1] = inv_I_plus_ldr_mul_ldr(Bt0, Bbt)
+                    Gt0[l + 1] = inv_invldr_plus_ldr(Bt0, Bbt)
+                    G0t[l + 1] = -inv_invldr_plus_ldr(Bbt, Bt0)
+                for a, b in zip(tmp, (Gtt[l + 1], Gt0[l + 1], G0t[l + 1])):
+                    worst = max(worst, self.check_error(a, b))
+        self.Gtt_all, self.Gt0_all, self.G0t_all = Gtt, Gt0, G0t
+        return worst
+
+    def half_wrap_unequal(self) -> np.ndarray:  # source/dqmc.cpp:288-315 with isUnequalTime_: [3, nt, N, N]
+        a, b = self.m.invexpK_half, self.m.expK_half
+        return np.stack([np.stack([a @ X[t] @ b for t in range(self.nt)]) for X in (self.Gtt_all, self.Gt0_all, self.G0t_all)])
+
 
 # ----------------------------------------------------------------------------------------------
 # Equal-time observables -- source/model.cpp:167-288
@@ -467,6 +509,43 @@ def observables(G: np.ndarray):
     # C(i,j) = n_i n_j + 2 (1 - G(j,i)) G(i,j) - navg^2   (note 1.0, not delta_ij: Q5; source/model.cpp:281)
     corr = np.outer(ni, ni) + 2.0 * (1.0 - G.T) * G - navg * navg
     return density, docc, swave, corr
+
+
+# ----------------------------------------------------------------------------------------------
+# Unequal-time observables -- source/model.cpp:290-392 (both spin species share G: factor 2 / square)
+# ----------------------------------------------------------------------------------------------
+def green_tau(Gt0: np.ndarray) -> np.ndarray:  # :290-313
+    return Gt0 + Gt0
+
+
+def doublon_tau(Gt0: np.ndarray) -> np.ndarray:  # :315-343
+    return Gt0 * Gt0
+
+
+def currxx_tau(Gtt: np.ndarray, Gt0: np.ndarray, G0t: np.ndarray, L1: int, L2: int) -> np.ndarray:  # :345-392
+    """[n_tau, N, N]; ix = +x neighbour of i (include/lattice.h:100-107)."""
+    n = L1 * L2
+    nx = np.array([site_neighbor(i, 1, 0, L1, L2) for i in range(n)])
+    idx = np.arange(n)
+    G00 = Gtt[0]
+    out = np.zeros_like(Gtt)
+    d1j = 2.0 * G00[nx, idx]  # dc_term1_j = G00(jx, j) up + dn
+    d2j = 2.0 * G00[idx, nx]  # dc_term2_j = G00(j, jx)
+    for t in range(Gtt.shape[0]):
+        d1i = 2.0 * Gtt[t][nx, idx]
+        d2i = 2.0 * Gtt[t][idx, nx]
+        A, Bm = G0t[t], Gt0[t]
+        # c_termK(i, j), up + dn = 2 x
+        c1 = 2.0 * A[nx][:, idx].T * Bm[nx][:, idx]          # G0t(jx, i) Gt0(ix, j)
+        c2 = 2.0 * A[idx][:, idx].T * Bm[nx][:, nx]          # G0t(j, i)  Gt0(ix, jx)
+        c3 = 2.0 * A[nx][:, nx].T * Bm[idx][:, idx]          # G0t(jx, ix) Gt0(i, j)
+        c4 = 2.0 * A[idx][:, nx].T * Bm[idx][:, nx]          # G0t(j, ix)  Gt0(i, jx)
+        t1 = np.outer(d1i, d1j) - c1
+        t2 = np.outer(d1i, d2j) - c2
+        t3 = np.outer(d2i, d1j) - c3
+        t4 = np.outer(d2i, d2j) - c4
+        out[t] = -(t1 - t2 - t3 + t4)
+    return out
 
 
 # ----------------------------------------------------------------------------------------------

@@ -78,9 +78,11 @@ class RefSim:
     """One reference chain: AttractiveHubbard + DQMC + GF + LDRStack built exactly as
     source/main.cpp:85-106 does, with an injected seed."""
 
-    def __init__(self, L1, L2, U, t, mu, beta, nt, n_stab, seed):
+    def __init__(self, L1, L2, U, t, mu, beta, nt, n_stab, seed, unequal=False):
         self.L = lib()
-        self.h = C.c_void_p(self.L.ref_create(L1, L2, U, t, mu, beta, nt, n_stab, seed))
+        self.L.ref_create_ex.restype = C.c_void_p
+        self.L.ref_create_ex.argtypes = [C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int, C.c_int, C.c_uint, C.c_int]
+        self.h = C.c_void_p(self.L.ref_create_ex(L1, L2, U, t, mu, beta, nt, n_stab, seed, int(bool(unequal))))
         if not self.h:
             raise RuntimeError("ref_create failed")
         self.ns = self.L.ref_ns(self.h)
@@ -205,6 +207,29 @@ class RefSim:
 
     def half_wrap(self):
         return self._mat(self.L.ref_half_wrap)
+
+    # --- unequal time (source/dqmc.cpp:223-280,458-514; needs unequal=True at construction) ---
+    def sweep_unequal(self):
+        self.L.ref_sweep_unequal(self.h)
+
+    def G_unequal(self, which: int, l: int) -> np.ndarray:
+        """which: 0 Gtt[l], 1 Gt0[l], 2 G0t[l]."""
+        buf = np.empty((self.ns, self.ns))
+        if self.L.ref_get_G_unequal(self.h, which, l, _d(buf)) != 0:
+            raise IndexError(f"G[{which}][{l}] not populated")
+        return _from_colmajor(buf)
+
+    def half_wrap_unequal(self) -> np.ndarray:
+        """[3, nt, N, N]: half-warped Gtt, Gt0, G0t for t < nt."""
+        buf = np.empty((3, self.nt, self.ns, self.ns))
+        self.L.ref_half_wrap_unequal(self.h, _d(buf))
+        return np.ascontiguousarray(np.swapaxes(buf, -1, -2))
+
+    def observables_tau(self):
+        """greenTau, doublonTau, currxxTau: [nt+1, N, N] each (source/model.cpp:290-392)."""
+        out = [np.empty((self.nt + 1, self.ns, self.ns)) for _ in range(3)]
+        self.L.ref_observables_tau(self.h, *[_d(o) for o in out])
+        return tuple(np.ascontiguousarray(np.swapaxes(o, -1, -2)) for o in out)
 
     def global_action(self):
         return self.L.ref_global_action(self.h)

@@ -74,7 +74,12 @@ extern "C" {
 
 void ref_set_blas_threads(int n) { scipy_openblas_set_num_threads(n); }
 
+void* ref_create_ex(int L1, int L2, double U, double t, double mu, double beta, int nt, int n_stab, unsigned seed, int unequal);
 void* ref_create(int L1, int L2, double U, double t, double mu, double beta, int nt, int n_stab, unsigned seed) {
+    return ref_create_ex(L1, L2, U, t, mu, beta, nt, n_stab, seed, 0);
+}
+// unequal != 0: [simulation] isMeasureUnequalTime = true (sweep_unequalTime active, source/dqmc.cpp:458-514)
+void* ref_create_ex(int L1, int L2, double U, double t, double mu, double beta, int nt, int n_stab, unsigned seed, int unequal) {
     scipy_openblas_set_num_threads(1);  // reference links mkl_sequential (CMakeLists.txt:27)
     char path[] = "/tmp/dqmc_ref_params_XXXXXX";
     int fd = mkstemp(path);
@@ -85,7 +90,8 @@ void* ref_create(int L1, int L2, double U, double t, double mu, double beta, int
         f << "[Lattice]\nL1 = " << L1 << "\nL2 = " << L2 << "\n[hubbard]\nU = " << U << "\nt = " << t
           << "\nmu = " << mu << "\n[simulation]\nbeta = " << beta << "\nnt = " << nt
           << "\nn_therms = 0\nn_sweeps = 1\nn_bins = 1\nn_stab = " << n_stab
-          << "\nsymmetric = false\nisMeasureUnequalTime = false\n[ParallelTempering]\nenabled = false\n";
+          << "\nsymmetric = false\nisMeasureUnequalTime = " << (unequal ? "true" : "false")
+          << "\n[ParallelTempering]\nenabled = false\n";
     }
     close(fd);
     Sim* s = new Sim();
@@ -173,6 +179,44 @@ void ref_sweep_bwd(void* h) {
     Sim* s = (Sim*)h;
     s->sim->sweep_beta_to_0(s->greens, s->stacks);
 }
+// DQMC::sweep_unequalTime (source/dqmc.cpp:458-514); which: 0 Gtt, 1 Gt0, 2 G0t
+void ref_sweep_unequal(void* h) {
+    Sim* s = (Sim*)h;
+    s->sim->sweep_unequalTime(s->greens, s->stacks);
+}
+int ref_get_G_unequal(void* h, int which, int l, double* out) {
+    Sim* s = (Sim*)h;
+    const std::vector<arma::mat>& v = which == 0 ? s->greens[0].Gtt : (which == 1 ? s->greens[0].Gt0 : s->greens[0].G0t);
+    if (l < 0 || l >= (int)v.size() || v[l].n_elem == 0) return 1;
+    copy_out(v[l], out);
+    return 0;
+}
+// DQMC::half_warp with unequal-time on (source/dqmc.cpp:288-315): out[3][nt][N*N] = sym Gtt, Gt0, G0t for t < nt
+void ref_half_wrap_unequal(void* h, double* out) {
+    Sim* s = (Sim*)h;
+    std::vector<GF> sym = s->greens;
+    s->sim->half_warp(sym, s->greens);
+    const int nt = s->model->nt(), nn = s->model->ns() * s->model->ns();
+    for (int t = 0; t < nt; ++t) {
+        copy_out(sym[0].Gtt[t], out + ((size_t)0 * nt + t) * nn);
+        copy_out(sym[0].Gt0[t], out + ((size_t)1 * nt + t) * nn);
+        copy_out(sym[0].G0t[t], out + ((size_t)2 * nt + t) * nn);
+    }
+}
+// Observables::calculate_{greenTau,doublonTau,currxxTau} (source/model.cpp:290-392): out[n_tau][N*N] each
+void ref_observables_tau(void* h, double* green, double* doublon, double* currxx) {
+    Sim* s = (Sim*)h;
+    const size_t nn = (size_t)s->model->ns() * s->model->ns();
+    const arma::cube g = Observables::calculate_greenTau(s->greens, *s->lat);
+    const arma::cube d = Observables::calculate_doublonTau(s->greens, *s->lat);
+    const arma::cube c = Observables::calculate_currxxTau(s->greens, *s->lat);
+    for (arma::uword t = 0; t < g.n_slices; ++t) {
+        copy_out(g.slice(t), green + t * nn);
+        copy_out(d.slice(t), doublon + t * nn);
+        copy_out(c.slice(t), currxx + t * nn);
+    }
+}
+
 double ref_acc_rate(void* h) { return ((Sim*)h)->sim->acc_rate(); }
 double ref_max_err(void* h) { return ((Sim*)h)->sim->max_err(); }
 double ref_mean_err(void* h) { return ((Sim*)h)->sim->mean_err(); }

@@ -215,6 +215,35 @@ def measure_case():
     np.savez_compressed(os.path.join(HERE, "measure.npz"), **out)
 
 
+def unequal_case():
+    """DQMC::sweep_unequalTime of the reference (isMeasureUnequalTime = true) after one full sweep on 4x4 and a
+    ragged 5x3 / nt=11 / n_stab=4 case: fields, the tape that produced them, every Gtt/Gt0/G0t, the three
+    tau observables, the half-warped arrays, and the MeasurementManager datasets with unequal-time on."""
+    out = {}
+    for name, cfg in (("a", (4, 4, 4.0, 1.0, -0.1, 2.0, 20, 5, 7)), ("b", (5, 3, 6.0, 1.0, 0.3, 2.0, 11, 4, 32))):
+        L1, L2, U, t, mu, beta, nt, n_stab, seed = cfg
+        s = ref.RefSim(*cfg, unequal=True)
+        out[f"{name}_cfg"] = np.array(cfg, dtype=np.float64)
+        out[f"{name}_fields0"] = s.fields().astype(np.int8)
+        perm, k, u = s.rng_tape(2 * nt)
+        out[f"{name}_perm"], out[f"{name}_k"], out[f"{name}_u"] = perm.astype(np.uint8), k.astype(np.uint8), u
+        tok = silence_stderr()
+        try:
+            s.sweep_fwd()
+            s.sweep_bwd()
+            s.sweep_unequal()
+        finally:
+            restore_stderr(tok)
+        out[f"{name}_fields"] = s.fields().astype(np.int8)
+        for wh, nm in enumerate(("Gtt", "Gt0", "G0t")):
+            out[f"{name}_{nm}"] = np.stack([s.G_unequal(wh, l) for l in range(nt + 1)])
+        g, d, c = s.observables_tau()
+        out[f"{name}_greenTau"], out[f"{name}_doublonTau"], out[f"{name}_currxxTau"] = g, d, c
+        out[f"{name}_half"] = s.half_wrap_unequal()
+        out[f"{name}_logdet"] = np.array(s.logdet())
+    np.savez_compressed(os.path.join(HERE, "unequal.npz"), **out)
+
+
 if __name__ == "__main__":
     assert ref.build(), "oracle/_ref could not be built (needs /root/reference)"
     for nm, cfg in CASES.items():
@@ -223,4 +252,5 @@ if __name__ == "__main__":
     misc_case()
     exchange_case()
     measure_case()
+    unequal_case()
     print("golden fixtures written to", HERE)

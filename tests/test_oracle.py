@@ -305,3 +305,34 @@ def test_measurement_transforms_golden():
     r = g["tf_6x6_r"]
     k = O.chi_r_to_chi_k(r, 6, 6)
     assert np.allclose(k[6 // 2 - 1, 6 // 2 - 1, :], r.sum(axis=(0, 1)))
+
+
+@pytest.mark.parametrize("name", ["a", "b"])
+def test_unequal_time_golden(name):
+    """oracle sweep_unequalTime / tau observables / half-warp vs the reference run with unequal-time on."""
+    g = load("unequal.npz")
+    L1, L2, U, t, mu, beta, nt, n_stab, seed = g[f"{name}_cfg"]
+    L1, L2, nt, n_stab = int(L1), int(L2), int(nt), int(n_stab)
+    m = O.Model(L1, L2, U, t, mu, beta, nt, fields=g[f"{name}_fields0"].astype(np.int64))
+    d = O.DQMC(m, n_stab)
+    d.init_stacks()
+    d.init_greenfunctions()
+    perm, k, u = g[f"{name}_perm"].astype(np.int64), g[f"{name}_k"].astype(np.int64), g[f"{name}_u"]
+    d.sweep_0_to_beta((perm[:nt], k[:nt], u[:nt]))
+    d.sweep_beta_to_0((perm[nt:], k[nt:], u[nt:]))
+    assert np.array_equal(m.fields, g[f"{name}_fields"])
+    worst = d.sweep_unequalTime()
+    assert worst < 1e-6
+    stab_points = {min((i + 1) * n_stab, nt) for i in range(d.n_stack)} | {0}
+    for nm, X in (("Gtt", d.Gtt_all), ("Gt0", d.Gt0_all), ("G0t", d.G0t_all)):
+        for l in range(nt + 1):
+            assert rel(X[l], g[f"{name}_{nm}"][l]) < (TOL if l in stab_points else 1e-7), (nm, l)
+    assert rel(O.green_tau(d.Gt0_all), g[f"{name}_greenTau"]) < 1e-7
+    assert rel(O.doublon_tau(d.Gt0_all), g[f"{name}_doublonTau"]) < 1e-7
+    assert rel(O.currxx_tau(d.Gtt_all, d.Gt0_all, d.G0t_all, L1, L2), g[f"{name}_currxxTau"]) < 1e-7
+    # the observable formulas themselves, teacher-forced on the reference's G's: tight
+    assert rel(O.green_tau(g[f"{name}_Gt0"]), g[f"{name}_greenTau"]) < 1e-14
+    assert rel(O.doublon_tau(g[f"{name}_Gt0"]), g[f"{name}_doublonTau"]) < 1e-14
+    assert rel(O.currxx_tau(g[f"{name}_Gtt"], g[f"{name}_Gt0"], g[f"{name}_G0t"], L1, L2), g[f"{name}_currxxTau"]) < 1e-13
+    assert rel(d.half_wrap_unequal(), g[f"{name}_half"]) < 1e-7
+    assert abs(d.log_det_M - float(g[f"{name}_logdet"])) < TOL * abs(d.log_det_M)

@@ -56,6 +56,7 @@ class DQMC {
     int nt_, n_stab_, n_stack_;
     bool mirror_stacks_ = true;
     double warned_err_ = 0.0;
+    double unequal_err_ = 0.0;
     std::vector<std::mt19937> extra_gens_;  // walkers 1.. of a batch (walker 0 follows model.rng())
 
     dqmcb_ctx* ctx() { return model_.ctx(); }
@@ -125,6 +126,7 @@ class DQMC {
         return which == 0 ? a[0] : (which == 1 ? m[0] : e[0]);
     }
     void mirror_stacks(bool on) { mirror_stacks_ = on; }
+    bool is_unequal_time() const { return isUnequalTime_; }
     int n_stack() const { return n_stack_; }
 
     // source/dqmc.cpp:43-59
@@ -154,7 +156,9 @@ class DQMC {
         (void)n;
         return greens;
     }
-    // source/dqmc.cpp:288-315 (equal-time entry)
+    // source/dqmc.cpp:288-315.  Equal-time: Gtt[0] of GF_asymm is half-warped.  With isMeasureUnequalTime the
+    // three arrays of the device's last sweep_unequalTime are half-warped for every t < nt (the reference
+    // transforms GF_asymm's host copies, which sweep_unequalTime below mirrors from the same device data).
     void half_warp(std::vector<GF>& GF_tosymm, std::vector<GF>& GF_asymm) {
         model_.upload_G(GF_asymm[0].Gtt[0]);
         const int n = model_.ns(), W = model_.n_walkers();
@@ -163,7 +167,18 @@ class DQMC {
         if (GF_tosymm[0].Gtt.empty()) GF_tosymm[0].Gtt.resize(nt_ + 1);
         GF_tosymm[0].Gtt[0].set_size(n, n);
         std::copy(out.begin(), out.begin() + (size_t)n * n, GF_tosymm[0].Gtt[0].memptr());
-        if (isUnequalTime_) throw std::runtime_error("half_warp: unequal-time Green's functions are not built in this version");
+        if (!isUnequalTime_) return;
+        GF_tosymm[0].Gtt.resize(nt_ + 1);
+        GF_tosymm[0].Gt0.resize(nt_ + 1);
+        GF_tosymm[0].G0t.resize(nt_ + 1);
+        for (int which = 0; which < 3; ++which) {
+            std::vector<arma::mat>& dst = which == 0 ? GF_tosymm[0].Gtt : (which == 1 ? GF_tosymm[0].Gt0 : GF_tosymm[0].G0t);
+            for (int t = (which == 0 ? 1 : 0); t < nt_; ++t) {
+                dqmcb::check(dqmcb_half_wrap_unequal(ctx(), which, t, out.data()), ctx(), "half_wrap_unequal");
+                dst[t].set_size(n, n);
+                std::copy(out.begin(), out.begin() + (size_t)n * n, dst[t].memptr());
+            }
+        }
     }
     // source/dqmc.cpp:337-396
     void sweep_0_to_beta(std::vector<GF>& greens, std::vector<LDRStack>& propagation_stacks) {
@@ -177,8 +192,32 @@ class DQMC {
         dqmcb::check(dqmcb_sweep_beta_to_0(ctx()), ctx(), "sweep_beta_to_0");
         after_sweep(greens, propagation_stacks, 0);
     }
-    // source/dqmc.cpp:458-514: no-op unless enabled, exactly like the reference's default configuration
-    void sweep_unequalTime(std::vector<GF>&, std::vector<LDRStack>&) {
-        if (isUnequalTime_) throw std::runtime_error("sweep_unequalTime: not built in this version (SURVEY.md 8f rank 2)");
+    // source/dqmc.cpp:458-514: no-op unless [simulation] isMeasureUnequalTime; otherwise the device computes
+    // G(tau,tau), G(tau,0), G(0,tau) for tau = 0..nt (stabilised at every block end) and walker 0's are
+    // mirrored into greens[0].Gtt / Gt0 / G0t like the reference fills them.  The stack is read-only.
+    void sweep_unequalTime(std::vector<GF>& greens, std::vector<LDRStack>&) {
+        if (!isUnequalTime_) return;
+        dqmcb::check(dqmcb_sweep_unequal_time(ctx()), ctx(), "sweep_unequal_time");
+        const int n = model_.ns(), W = model_.n_walkers();
+        std::vector<double> buf((size_t)W * n * n);
+        greens[0].Gtt.resize(nt_ + 1);
+        greens[0].Gt0.resize(nt_ + 1);
+        greens[0].G0t.resize(nt_ + 1);
+        for (int which = 0; which < 3; ++which) {
+            std::vector<arma::mat>& dst = which == 0 ? greens[0].Gtt : (which == 1 ? greens[0].Gt0 : greens[0].G0t);
+            for (int l = 0; l <= nt_; ++l) {
+                dqmcb::check(dqmcb_get_G_unequal(ctx(), which, l, buf.data()), ctx(), "get_G_unequal");
+                dst[l].set_size(n, n);
+                std::copy(buf.begin(), buf.begin() + (size_t)n * n, dst[l].memptr());
+            }
+        }
+        std::vector<double> ld(W), err(W);
+        dqmcb::check(dqmcb_get_logdet(ctx(), ld.data()), ctx(), "get_logdet");
+        greens[0].log_det_M = ld[0];
+        dqmcb::check(dqmcb_get_unequal_err(ctx(), err.data()), ctx(), "get_unequal_err");
+        unequal_err_ = err[0];
+        if (err[0] > 1e-6)  // source/dqmc.cpp:505-508
+            std::cerr << "WARNING: GF unequaltime precision > 1e-6. Reduce n_stab or increasing nt. Error: " << err[0] << std::endl;
     }
+    double unequal_err() const { return unequal_err_; }
 };

@@ -151,8 +151,15 @@ class MeasurementManager {
         EqTimeFn fn;
         arma::mat sum;
     };
+    struct UneqTime {
+        std::string name;
+        UneqTimeFn fn;
+        arma::cube sum;
+    };
     std::vector<Scalar> scalars_;
     std::vector<EqTime> eqtime_;
+    std::vector<UneqTime> uneqtime_;
+    long long dev_tau_count_ = 0;
     int rank_;
     bool unequal_;
     int host_count_ = 0;      // measure() calls in the open bin
@@ -178,8 +185,9 @@ class MeasurementManager {
 
     void addScalar(const std::string& name, ScalarFn fn) { scalars_.push_back({name, std::move(fn), 0.0}); }
     void addEqualTime(const std::string& name, EqTimeFn fn) { eqtime_.push_back({name, std::move(fn), arma::mat()}); }
-    void addUnequalTime(const std::string&, UneqTimeFn) {
-        if (unequal_) throw std::runtime_error("addUnequalTime: unequal-time measurements are not built in this version (SURVEY.md 8f rank 2)");
+    void addUnequalTime(const std::string& name, UneqTimeFn fn) {  // ignored unless isMeasureUnequalTime (:181-187)
+        if (!unequal_) return;
+        uneqtime_.push_back({name, std::move(fn), arma::cube()});
     }
 
     // reference semantics: one sample per call from the host Green's functions (include/measurementh5.h:189-229)
@@ -191,6 +199,16 @@ class MeasurementManager {
                 e.sum = r;
             } else {
                 for (arma::uword i = 0; i < r.n_elem; ++i) e.sum(i) += r(i);
+            }
+        }
+        if (unequal_) {
+            for (auto& u : uneqtime_) {
+                arma::cube r = u.fn(greens, lat);
+                if (u.sum.n_elem == 0) {
+                    u.sum = r;
+                } else {
+                    for (arma::uword i = 0; i < r.n_elem; ++i) u.sum.memptr()[i] += r.memptr()[i];
+                }
             }
         }
         ++host_count_;
@@ -206,6 +224,10 @@ class MeasurementManager {
         }
         dqmcb::check(dqmcb_bin_measure(model.ctx()), model.ctx(), "bin_measure");
         dev_count_ += model.n_walkers();
+        if (unequal_) {  // greenTau, doublonTau, currxxTau of the sweep_unequalTime that preceded this call
+            dqmcb::check(dqmcb_bin_measure_unequal(model.ctx()), model.ctx(), "bin_measure_unequal");
+            dev_tau_count_ += model.n_walkers();
+        }
     }
 
     // include/measurementh5.h:231-274 (+ saveToHDF5 :276-361)
@@ -222,6 +244,12 @@ class MeasurementManager {
                 emit_equal_time(bin_r, bin_k, e.name, transform::chi_site_to_chi_r(e.sum, lat));
                 e.sum.zeros();
             }
+            for (auto& u : uneqtime_) {
+                if (u.sum.n_elem == 0) continue;
+                for (arma::uword i = 0; i < u.sum.n_elem; ++i) u.sum.memptr()[i] /= host_count_;
+                emit_cube(bin_r, bin_k, "/unequaltime/", u.name, transform::chi_site_to_chi_r(u.sum, lat));
+                u.sum.zeros();
+            }
         }
         if (dev_model_ && dev_count_ > 0) {
             const int n = lat.L1() * lat.L2();
@@ -234,6 +262,19 @@ class MeasurementManager {
             for (int i = 0; i < n; ++i) chi_r.memptr()[i] /= (double)cnt;
             emit_equal_time(bin_r, bin_k, "densityCorr", chi_r);
             dev_count_ = 0;
+            if (dev_tau_count_ > 0) {
+                const int nt1 = dev_model_->nt() + 1;
+                std::vector<double> sums((size_t)3 * nt1 * n);
+                long long c2 = 0;
+                dqmcb::check(dqmcb_bin_fetch_unequal(dev_model_->ctx(), sums.data(), &c2, 1), dev_model_->ctx(), "bin_fetch_unequal");
+                static const char* tnames[3] = {"greenTau", "doublonTau", "currxxTau"};  // source/main.cpp:120-122
+                for (int k = 0; k < 3; ++k) {
+                    arma::cube cube(lat.L1(), lat.L2(), nt1);
+                    for (size_t i = 0; i < (size_t)nt1 * n; ++i) cube.memptr()[i] = sums[(size_t)k * nt1 * n + i] / (double)c2;
+                    emit_cube(bin_r, bin_k, "/unequaltime/", tnames[k], cube);
+                }
+                dev_tau_count_ = 0;
+            }
         }
 #ifdef DQMCB_USE_HDF5
         write_bin_hdf5(bin_r, bin_k);
@@ -249,13 +290,17 @@ class MeasurementManager {
    private:
     size_t hdf5_written_ = 0;
     void emit_equal_time(const std::string& bin_r, const std::string& bin_k, const std::string& name, const arma::cube& chi_r) {
-        store_.put_cube(bin_r + "/equaltime/" + name, chi_r);
+        emit_cube(bin_r, bin_k, "/equaltime/", name, chi_r);
+    }
+    void emit_cube(const std::string& bin_r, const std::string& bin_k, const std::string& group, const std::string& name,
+                   const arma::cube& chi_r) {
+        store_.put_cube(bin_r + group + name, chi_r);
         // k-space needs the lattice only for L1, L2: rebuild the k-grid on the device from the cube's shape
         arma::cx_cube chi_k(chi_r.n_rows, chi_r.n_cols, chi_r.n_slices);
         dqmcb::check(dqmcb_chi_r_to_chi_k(0, (int)chi_r.n_rows, (int)chi_r.n_cols, (int)chi_r.n_slices, chi_r.memptr(),
                                           reinterpret_cast<double*>(chi_k.memptr())),
                      nullptr, "chi_r_to_chi_k");
-        store_.put_complex_cube(bin_k + "/equaltime/" + name, chi_k);
+        store_.put_complex_cube(bin_k + group + name, chi_k);
     }
 #ifdef DQMCB_USE_HDF5
     // the reference's group tree (include/measurementh5.h:294-312): every bin has scalar / equaltime /

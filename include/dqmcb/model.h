@@ -225,4 +225,21 @@ inline arma::mat calculate_densityCorr(AttractiveHubbard& model, const std::vect
     detail::measure(model, greens, s, &c);
     return c;
 }
+// source/model.cpp:290-392.  Evaluated on the device from the arrays of the last DQMC::sweep_unequalTime (the
+// host copies in `greens` are mirrors of the same data): (N, N, nt+1) cubes of walker 0.
+namespace detail {
+inline arma::cube tau_cube(AttractiveHubbard& model, const Lattice& lat, int which) {
+    const int W = model.n_walkers(), n = model.ns(), nt1 = model.nt() + 1;
+    std::vector<double> buf((size_t)W * nt1 * n * n);
+    double* outs[3] = {nullptr, nullptr, nullptr};
+    outs[which] = buf.data();
+    dqmcb::check(dqmcb_measure_unequal_time(model.ctx(), lat.L1(), lat.L2(), outs[0], outs[1], outs[2]), model.ctx(), "measure_unequal_time");
+    arma::cube c(n, n, nt1);
+    std::copy(buf.begin(), buf.begin() + (size_t)nt1 * n * n, c.memptr());
+    return c;
+}
+}  // namespace detail
+inline arma::cube calculate_greenTau(AttractiveHubbard& model, const std::vector<GF>&, const Lattice& lat) { return detail::tau_cube(model, lat, 0); }
+inline arma::cube calculate_doublonTau(AttractiveHubbard& model, const std::vector<GF>&, const Lattice& lat) { return detail::tau_cube(model, lat, 1); }
+inline arma::cube calculate_currxxTau(AttractiveHubbard& model, const std::vector<GF>&, const Lattice& lat) { return detail::tau_cube(model, lat, 2); }
 }  // namespace Observables

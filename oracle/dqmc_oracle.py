@@ -618,9 +618,10 @@ class MeasurementManager:
     /bin_<n>/equaltime/densityCorr [L1, L2, 1], /binK_<n>/equaltime/densityCorr [L1, L2, 1, 2]."""
 
     SCALARS = ("density", "doubleOcc", "swave")
+    UNEQUAL = ("greenTau", "doublonTau", "currxxTau")  # source/main.cpp:120-122, only with isMeasureUnequalTime
 
-    def __init__(self, L1: int, L2: int):
-        self.L1, self.L2 = L1, L2
+    def __init__(self, L1: int, L2: int, unequal: bool = False):
+        self.L1, self.L2, self.unequal = L1, L2, unequal
         self.bin = 0
         self.datasets: dict = {}
         self._reset()
@@ -629,6 +630,12 @@ class MeasurementManager:
         self.scal = np.zeros(3)
         self.corr = None
         self.count = 0
+        self.tau = None
+
+    def measure_unequal(self, Gtt, Gt0, G0t) -> None:  # :189-229 with the unequal-time calculators
+        self.measure(Gtt[0])
+        cubes = [green_tau(Gt0), doublon_tau(Gt0), currxx_tau(Gtt, Gt0, G0t, self.L1, self.L2)]
+        self.tau = cubes if self.tau is None else [a + b for a, b in zip(self.tau, cubes)]
 
     def measure(self, G: np.ndarray) -> None:  # :189-229
         d, o, s, corr = observables(G)
@@ -646,6 +653,12 @@ class MeasurementManager:
             chi_k = chi_r_to_chi_k(chi_r, self.L1, self.L2)
             self.datasets[f"/bin_{b}/equaltime/densityCorr"] = chi_r
             self.datasets[f"/binK_{b}/equaltime/densityCorr"] = np.stack([chi_k.real, chi_k.imag], axis=-1)
+        if self.tau is not None:
+            for name, cube in zip(self.UNEQUAL, self.tau):
+                chi_r = chi_site_to_chi_r(cube / self.count, self.L1, self.L2)
+                chi_k = chi_r_to_chi_k(chi_r, self.L1, self.L2)
+                self.datasets[f"/bin_{b}/unequaltime/{name}"] = chi_r
+                self.datasets[f"/binK_{b}/unequaltime/{name}"] = np.stack([chi_k.real, chi_k.imag], axis=-1)
         self._reset()
         self.bin += 1
 

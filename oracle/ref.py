@@ -356,10 +356,11 @@ class RefMeasure:
     unmodified over the HDF5 recorder shim (oracle/ref_measure.cpp).  `datasets()` returns what
     results/data_<rank>.h5 would contain: {path: ndarray with the dataset's dims, C order}."""
 
-    def __init__(self, L1: int, L2: int, rank: int = 0):
+    def __init__(self, L1: int, L2: int, rank: int = 0, unequal: bool = False):
         L = lib()
-        L.refm_create.restype = C.c_void_p
-        L.refm_create.argtypes = [C.c_int, C.c_int, C.c_int]
+        L.refm_create_ex.restype = C.c_void_p
+        L.refm_create_ex.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int]
+        L.refm_measure_unequal.argtypes = [C.c_void_p, C.c_int, _dp, _dp, _dp]
         for name in ("refm_destroy", "refm_accumulate"):
             getattr(L, name).argtypes = [C.c_void_p]
         L.refm_measure.argtypes = [C.c_void_p, _dp]
@@ -369,7 +370,7 @@ class RefMeasure:
         L.refm_chi_site_to_chi_r.argtypes = [C.c_void_p, C.c_int, _dp, _dp]
         L.refm_chi_r_to_chi_k.argtypes = [C.c_void_p, C.c_int, _dp, _dp]
         self.L, self.L1, self.L2, self.N = L, L1, L2, L1 * L2
-        self.h = L.refm_create(L1, L2, rank)
+        self.h = L.refm_create_ex(L1, L2, rank, int(bool(unequal)))
         if not self.h:
             raise RuntimeError("refm_create failed")
 
@@ -381,6 +382,11 @@ class RefMeasure:
     def measure(self, G: np.ndarray) -> None:
         g = np.asfortranarray(G, dtype=np.float64)  # arma::mat is column-major
         self.L.refm_measure(self.h, g.ctypes.data_as(_dp))
+
+    def measure_unequal(self, Gtt, Gt0, G0t) -> None:
+        """measure() with the full GF of an unequal-time run: arrays [n_tau, N, N]."""
+        bufs = [np.ascontiguousarray(np.swapaxes(np.asarray(x, dtype=np.float64), -1, -2)) for x in (Gtt, Gt0, G0t)]
+        self.L.refm_measure_unequal(self.h, bufs[0].shape[0], *[b.ctypes.data_as(_dp) for b in bufs])
 
     def accumulate(self) -> None:
         self.L.refm_accumulate(self.h)

@@ -43,13 +43,16 @@ arma::mat mat_in2(int r, int c, const double* p) {
 extern "C" {
 
 // MeasurementManager wired as in source/main.cpp:114-119 for an L1 x L2 square lattice
-void* refm_create(int L1, int L2, int rank) {
+void* refm_create_ex(int L1, int L2, int rank, int unequal);
+void* refm_create(int L1, int L2, int rank) { return refm_create_ex(L1, L2, rank, 0); }
+// unequal != 0: isMeasureUnequalTime = true and greenTau / doublonTau / currxxTau registered (source/main.cpp:120-122)
+void* refm_create_ex(int L1, int L2, int rank, int unequal) {
     char path[] = "/tmp/dqmc_refm_params_XXXXXX";
     int fd = mkstemp(path);
     if (fd < 0) return nullptr;
     {
         std::ofstream f(path);
-        f << "[Lattice]\nL1 = " << L1 << "\nL2 = " << L2 << "\n[simulation]\nisMeasureUnequalTime = false\n";
+        f << "[Lattice]\nL1 = " << L1 << "\nL2 = " << L2 << "\n[simulation]\nisMeasureUnequalTime = " << (unequal ? "true" : "false") << "\n";
     }
     close(fd);
     MeasSim* s = new MeasSim();
@@ -64,6 +67,9 @@ void* refm_create(int L1, int L2, int rank) {
         s->mgr->addScalar("doubleOcc", Observables::calculate_doubleOccupancy);
         s->mgr->addScalar("swave", Observables::calculate_swavePairing);
         s->mgr->addEqualTime("densityCorr", Observables::calculate_densityCorr);
+        s->mgr->addUnequalTime("greenTau", Observables::calculate_greenTau);
+        s->mgr->addUnequalTime("doublonTau", Observables::calculate_doublonTau);
+        s->mgr->addUnequalTime("currxxTau", Observables::calculate_currxxTau);
         h5shim::store() = h5shim::State();
     } catch (const std::exception& e) {
         std::fprintf(stderr, "refm_create: %s\n", e.what());
@@ -82,6 +88,22 @@ void refm_measure(void* h, const double* G) {
     std::vector<GF> greens(1);
     greens[0].Gtt.resize(1);
     greens[0].Gtt[0] = mat_in2(n, n, G);
+    s->mgr->measure(greens, *s->lat);
+}
+
+// measure with the full unequal-time GF: Gtt, Gt0, G0t = [n_tau][N*N] column-major each
+void refm_measure_unequal(void* h, int n_tau, const double* Gtt, const double* Gt0, const double* G0t) {
+    MeasSim* s = (MeasSim*)h;
+    const int n = s->lat->n_sites();
+    std::vector<GF> greens(1);
+    greens[0].Gtt.resize(n_tau);
+    greens[0].Gt0.resize(n_tau);
+    greens[0].G0t.resize(n_tau);
+    for (int t = 0; t < n_tau; ++t) {
+        greens[0].Gtt[t] = mat_in2(n, n, Gtt + (size_t)t * n * n);
+        greens[0].Gt0[t] = mat_in2(n, n, Gt0 + (size_t)t * n * n);
+        greens[0].G0t[t] = mat_in2(n, n, G0t + (size_t)t * n * n);
+    }
     s->mgr->measure(greens, *s->lat);
 }
 

@@ -7,6 +7,7 @@
 //   host_mirror_test traj  L1 L2 U t mu beta nt n_stab seed n_sweeps out.txt
 //   host_mirror_test exchange out.txt         (4-replica beta ladder of tests/golden/exchange.npz)
 //   host_mirror_test api out.txt              (stablelinalg / containers / error behaviour)
+//   host_mirror_test unequal L1 L2 U t mu beta nt n_stab seed out.txt   (isMeasureUnequalTime = true)
 //   host_mirror_test measure in.txt out.txt   (MeasurementManager / transform:: on the G's of tests/golden/measure.npz)
 #include <cstdio>
 #include <cstdlib>
@@ -276,17 +277,6 @@ static int run_measure(int argc, char** argv) {
     dump(f, "tf_k", reinterpret_cast<const double*>(k.memptr()), 2 * k.n_elem);
     double meta[3] = {(double)host_mm.current_bin(), (double)transform::pbc_shortest(4, 6), (double)transform::pbc_shortest(-3, 6)};
     dump(f, "meta", meta, 3);
-    int threw = 0;
-    try {
-        utility::parameters p2 = make_params(L, L, 4.0, 1.0, -0.1, 2.0, 20, 5);
-        p2.set("simulation", "isMeasureUnequalTime", "true");
-        MeasurementManager m3(p2, 0, 0);
-        m3.addUnequalTime("greenTau", [](const std::vector<GF>&, const Lattice&) { return arma::cube(); });
-    } catch (const std::runtime_error&) {
-        threw = 1;
-    }
-    double th = threw;
-    dump(f, "unequal_throws", &th, 1);
 #ifdef DQMCB_USE_HDF5
     // built against the HDF5 recorder shim (oracle/shim/hdf5.h): what the HDF5 branch of the mirror wrote
     for (const auto& d : h5shim::store().sets) {
@@ -301,6 +291,69 @@ static int run_measure(int argc, char** argv) {
     return 0;
 }
 
+// Unequal-time run wired as source/main.cpp:156-170 with isMeasureUnequalTime = true: one full sweep,
+// sweep_unequalTime, half_warp, measure (host calculators and device bins), accumulate.
+static int run_unequal(int argc, char** argv) {
+    if (argc < 12) return 2;
+    const int L1 = atoi(argv[2]), L2 = atoi(argv[3]);
+    const double U = atof(argv[4]), t = atof(argv[5]), mu = atof(argv[6]), beta = atof(argv[7]);
+    const int nt = atoi(argv[8]), n_stab = atoi(argv[9]);
+    const unsigned seed = (unsigned)atol(argv[10]);
+    FILE* f = fopen(argv[11], "w");
+    if (!f) return 3;
+    utility::parameters params = make_params(L1, L2, U, t, mu, beta, nt, n_stab);
+    params.set("simulation", "isMeasureUnequalTime", "true");
+    utility::random rng(seed);
+    Lattice lat(params, {1.0, 0.0}, {0.0, 1.0}, {{0.0, 0.0}});
+    AttractiveHubbard model(params, lat, rng, beta);
+    DQMC sim(params, model);
+    std::vector<LDRStack> stacks(1);
+    std::vector<GF> greens(1);
+    stacks[0] = sim.init_stacks(0);
+    greens[0] = sim.init_greenfunctions(stacks[0]);
+    MeasurementManager host_mm(params, 0, 0), dev_mm(params, 0, 0);
+    host_mm.addScalar("density", [&](const std::vector<GF>& g, const Lattice& l) { return Observables::calculate_density(model, g, l); });
+    host_mm.addScalar("doubleOcc", [&](const std::vector<GF>& g, const Lattice& l) { return Observables::calculate_doubleOccupancy(model, g, l); });
+    host_mm.addScalar("swave", [&](const std::vector<GF>& g, const Lattice& l) { return Observables::calculate_swavePairing(model, g, l); });
+    host_mm.addEqualTime("densityCorr", [&](const std::vector<GF>& g, const Lattice& l) { return Observables::calculate_densityCorr(model, g, l); });
+    host_mm.addUnequalTime("greenTau", [&](const std::vector<GF>& g, const Lattice& l) { return Observables::calculate_greenTau(model, g, l); });
+    host_mm.addUnequalTime("doublonTau", [&](const std::vector<GF>& g, const Lattice& l) { return Observables::calculate_doublonTau(model, g, l); });
+    host_mm.addUnequalTime("currxxTau", [&](const std::vector<GF>& g, const Lattice& l) { return Observables::calculate_currxxTau(model, g, l); });
+    sim.sweep_0_to_beta(greens, stacks);
+    sim.sweep_beta_to_0(greens, stacks);
+    sim.sweep_unequalTime(greens, stacks);
+    dump_fields(f, "fields", model.fields().fields());
+    for (int l = 0; l <= nt; ++l) {
+        dump_mat(f, "Gtt_" + std::to_string(l), greens[0].Gtt[l]);
+        dump_mat(f, "Gt0_" + std::to_string(l), greens[0].Gt0[l]);
+        dump_mat(f, "G0t_" + std::to_string(l), greens[0].G0t[l]);
+    }
+    dump(f, "logdet", &greens[0].log_det_M, 1);
+    const double ue = sim.unequal_err();
+    dump(f, "unequal_err", &ue, 1);
+    std::vector<GF> sym = greens;
+    sim.half_warp(sym, greens);
+    for (int l : {0, 1, nt - 1}) {
+        dump_mat(f, "symGtt_" + std::to_string(l), sym[0].Gtt[l]);
+        dump_mat(f, "symGt0_" + std::to_string(l), sym[0].Gt0[l]);
+        dump_mat(f, "symG0t_" + std::to_string(l), sym[0].G0t[l]);
+    }
+    host_mm.measure(greens, lat);
+    dev_mm.measure_device(model, lat);
+    host_mm.accumulate(lat);
+    dev_mm.accumulate(lat);
+    for (const auto* mm : {&host_mm, &dev_mm}) {
+        const std::string tag = (mm == &host_mm) ? "A:" : "B:";
+        for (const auto& d : mm->store().datasets()) {
+            dump(f, tag + d.path, d.data.data(), d.data.size());
+            std::vector<double> dims(d.dims.begin(), d.dims.end());
+            dump(f, tag + "dims:" + d.path, dims.data(), dims.size());
+        }
+    }
+    fclose(f);
+    return 0;
+}
+
 int main(int argc, char** argv) {
     if (argc < 2) return 2;
     try {
@@ -308,6 +361,7 @@ int main(int argc, char** argv) {
         if (!strcmp(argv[1], "exchange")) return run_exchange(argc, argv);
         if (!strcmp(argv[1], "api")) return run_api(argc, argv);
         if (!strcmp(argv[1], "measure")) return run_measure(argc, argv);
+        if (!strcmp(argv[1], "unequal")) return run_unequal(argc, argv);
     } catch (const std::exception& e) {
         fprintf(stderr, "host_mirror_test: %s\n", e.what());
         return 1;

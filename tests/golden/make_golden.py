@@ -241,6 +241,15 @@ def unequal_case():
         out[f"{name}_greenTau"], out[f"{name}_doublonTau"], out[f"{name}_currxxTau"] = g, d, c
         out[f"{name}_half"] = s.half_wrap_unequal()
         out[f"{name}_logdet"] = np.array(s.logdet())
+        if L1 == L2:  # MeasurementManager with unequal-time on (k-space of the reference needs a square lattice)
+            mm = ref.RefMeasure(L1, L2, rank=0, unequal=True)
+            mm.measure_unequal(out[f"{name}_Gtt"], out[f"{name}_Gt0"], out[f"{name}_G0t"])
+            mm.accumulate()
+            ds = mm.datasets()
+            out[f"{name}_paths"] = np.array(list(ds.keys()))
+            for k2, v in ds.items():
+                out[f"{name}_ds:" + k2] = v
+            mm.close()
     np.savez_compressed(os.path.join(HERE, "unequal.npz"), **out)
 
 

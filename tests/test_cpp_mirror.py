@@ -159,4 +159,36 @@ def test_measurement_manager_mirror(variant, tmp_path):
     z = o["tf_k"][0::2] + 1j * o["tf_k"][1::2]
     assert np.max(np.abs(z.reshape((6, 6, 2), order="F") - want_k)) < 1e-12 * np.max(np.abs(want_k))
     assert list(o["meta"]) == [2, O.pbc_shortest(4, 6), O.pbc_shortest(-3, 6)]
-    assert o["unequal_throws"][0] == 1
+
+
+@pytest.mark.gpu
+def test_unequal_time_mirror_reproduces_reference(tmp_path):
+    """Reference-style main with isMeasureUnequalTime = true (source/main.cpp:156-170): same seed -> same fields;
+    Gtt/Gt0/G0t of every slice, half-warps and the full dataset tree (host calculators and device bins) against
+    the reference run behind tests/golden/unequal.npz.  1e-10 at stabilisation points, drift envelope between."""
+    g = np.load(os.path.join(GOLD, "unequal.npz"))
+    L1, L2, U, t, mu, beta, nt, n_stab, seed = g["a_cfg"]
+    L1, L2, nt, n_stab, seed = int(L1), int(L2), int(nt), int(n_stab), int(seed)
+    n = L1 * L2
+    r, out = run(["unequal", L1, L2, U, t, mu, beta, nt, n_stab, seed], tmp_path)
+    assert r.returncode == 0, r.stderr
+    o = parse(out)
+    cm = lambda v: v.reshape(n, n).T
+    assert np.array_equal(o["fields"].reshape(n, nt).T.astype(np.int64), g["a_fields"])
+    stab = {min((i + 1) * n_stab, nt) for i in range(-(-nt // n_stab))} | {0}
+    for nm in ("Gtt", "Gt0", "G0t"):
+        for l in range(nt + 1):
+            assert rel(cm(o[f"{nm}_{l}"]), g[f"a_{nm}"][l]) < (1e-10 if l in stab else 1e-7), (nm, l)
+    assert abs(o["logdet"][0] - float(g["a_logdet"])) < 1e-10 * abs(float(g["a_logdet"]))
+    assert o["unequal_err"][0] < 1e-6
+    for wh, nm in enumerate(("Gtt", "Gt0", "G0t")):
+        for l in (0, 1, nt - 1):
+            assert rel(cm(o[f"sym{nm}_{l}"]), g["a_half"][wh, l]) < 1e-7, (nm, l)
+    paths = [str(p) for p in g["a_paths"]]
+    for tag in ("A:", "B:"):
+        got = [k[len(tag):] for k in o if k.startswith(tag) and not k.startswith(tag + "dims:")]
+        assert sorted(got) == sorted(paths), tag
+        for p in paths:
+            want = g["a_ds:" + p]
+            assert [int(x) for x in o[tag + "dims:" + p]] == list(want.shape), (tag, p)
+            assert rel(o[tag + p].reshape(want.shape), want) < (1e-10 if "unequal" not in p else 1e-7), (tag, p)

@@ -336,3 +336,18 @@ def test_unequal_time_golden(name):
     assert rel(O.currxx_tau(g[f"{name}_Gtt"], g[f"{name}_Gt0"], g[f"{name}_G0t"], L1, L2), g[f"{name}_currxxTau"]) < 1e-13
     assert rel(d.half_wrap_unequal(), g[f"{name}_half"]) < 1e-7
     assert abs(d.log_det_M - float(g[f"{name}_logdet"])) < TOL * abs(d.log_det_M)
+
+
+def test_measurement_manager_unequal_golden():
+    """MeasurementManager with isMeasureUnequalTime: /bin_0/unequaltime/* [L1, L2, nt+1] and
+    /binK_0/unequaltime/* [L1, L2, nt+1, 2] as the reference recorded them, teacher-forced on its G's."""
+    g = load("unequal.npz")
+    mm = O.MeasurementManager(4, 4, unequal=True)
+    mm.measure_unequal(g["a_Gtt"], g["a_Gt0"], g["a_G0t"])
+    mm.accumulate()
+    paths = [str(p) for p in g["a_paths"]]
+    assert sorted(paths) == sorted(mm.datasets) and len(paths) == 11
+    for p in paths:
+        want = g["a_ds:" + p]
+        assert mm.datasets[p].shape == want.shape, p
+        assert rel(mm.datasets[p], want) < 1e-12, p

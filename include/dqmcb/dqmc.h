@@ -6,6 +6,8 @@
 //   * after sweep_0_to_beta   greens[0].Gtt[nt] and log_det_M are current (reference: source/dqmc.cpp:383),
 //     after sweep_beta_to_0   greens[0].Gtt[0]  and log_det_M are current (source/dqmc.cpp:443);
 //     the intermediate Gtt[l] of the reference (touched two-adjacent-at-a-time) are not materialised;
+//   * with [simulation] isMeasureUnequalTime, sweep_unequalTime fills greens[0].Gtt / Gt0 / G0t [0..nt]
+//     from the device (source/dqmc.cpp:458-514) and half_warp transforms all three (source/dqmc.cpp:303-312);
 //   * model.fields() and every stack entry are refreshed after each sweep (mirror_stacks(false)
 //     turns the stack copy off for throughput runs);
 //   * the random stream is drawn from model.rng() with the reference's own libstdc++ calls

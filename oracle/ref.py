@@ -430,3 +430,19 @@ class RefMeasure:
 
     def pbc_shortest(self, d: int, L: int) -> int:
         return int(self.L.refm_pbc_shortest(d, L))
+
+
+def params_query(path: str, section: str, key: str, kind: int):
+    """utility::parameters of the reference on `path`: kind 0 string, 1 int, 2 double, 3 bool, 4 vector,
+    5 hasSection, 6 hasKey.  Returns the value, or RuntimeError when the reference throws."""
+    L = lib()
+    L.ref_params_query.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_int, _dp, C.c_char_p, C.c_int]
+    num = np.zeros(32)
+    buf = C.create_string_buffer(1024)
+    if L.ref_params_query(path.encode(), section.encode(), key.encode(), kind, _d(num), buf, 1024) != 0:
+        raise RuntimeError("reference parser threw")
+    if kind == 0:
+        return buf.value.decode()
+    if kind == 4:
+        return list(num[1:1 + int(num[0])])
+    return {1: int, 2: float, 3: bool, 5: bool, 6: bool}[kind](num[0])

@@ -217,6 +217,31 @@ void ref_observables_tau(void* h, double* green, double* doublon, double* currxx
     }
 }
 
+// utility::parameters (include/utility.h:50-276) on a file: kind 0 getString, 1 getInt, 2 getDouble, 3 getBool,
+// 4 getDoubleVector (num[0] = count, values follow), 5 hasSection, 6 hasKey.  Returns 0, or 1 on std::runtime_error.
+int ref_params_query(const char* path, const char* section, const char* key, int kind, double* num, char* str, int cap) {
+    try {
+        utility::parameters p(path);
+        switch (kind) {
+            case 0: std::snprintf(str, cap, "%s", p.getString(section, key).c_str()); break;
+            case 1: num[0] = p.getInt(section, key); break;
+            case 2: num[0] = p.getDouble(section, key); break;
+            case 3: num[0] = p.getBool(section, key) ? 1.0 : 0.0; break;
+            case 4: {
+                const std::vector<double> v = p.getDoubleVector(section, key);
+                num[0] = (double)v.size();
+                for (size_t i = 0; i < v.size() && i < 30; ++i) num[1 + i] = v[i];
+                break;
+            }
+            case 5: num[0] = p.hasSection(section) ? 1.0 : 0.0; break;
+            default: num[0] = p.hasKey(section, key) ? 1.0 : 0.0; break;
+        }
+    } catch (const std::runtime_error&) {
+        return 1;
+    }
+    return 0;
+}
+
 double ref_acc_rate(void* h) { return ((Sim*)h)->sim->acc_rate(); }
 double ref_max_err(void* h) { return ((Sim*)h)->sim->max_err(); }
 double ref_mean_err(void* h) { return ((Sim*)h)->sim->mean_err(); }

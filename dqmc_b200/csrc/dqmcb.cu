@@ -955,8 +955,42 @@ static int grouped_sweep(dqmcb_ctx* ctx, int dir) {
             if (p.rng_mode != DQMCB_RNG_TAPE) p.visit_base = 0;
             // visits are consumed in sweep order: slice l is visit (l) forward, (nt-1-l) backward
             const unsigned long long vfirst = v0 + (unsigned long long)((dir > 0) ? l0 : (p0.nt - l1));
-            if (fast64_propagate(ctx, p, (dir > 0) ? l0 : l1 - 1, l1 - l0, dir, vfirst, 3, ctx->gstream[g])) return DQMCB_ECUDA;
-            fast_stabilize(ctx, (dir > 0) ? l1 - 1 : l0, dir, p.w0, p.w1, ctx->gstream[g]);
+            static const bool dbg = getenv("DQMCB_DEBUG_SYNC") != nullptr;  // development aid: localise a faulting launch
+            static const int gmode = getenv("DQMCB_GROUP_DBG") ? atoi(getenv("DQMCB_GROUP_DBG")) : 0;
+            cudaStream_t gs = (gmode == 2) ? ctx->gstream[0] : ctx->gstream[g];
+            if (gmode == 1 && !(b == 0 && g == 0)) {  // chain the groups: no overlap, no host sync
+                const int pg = (g + ng - 1) % ng;
+                CK(cudaStreamWaitEvent(gs, ctx->gdone[pg], 0));
+            }
+            static cudaEvent_t ev_p[8] = {}, ev_s[8] = {};
+            if ((gmode == 3 || gmode == 4) && !ev_p[0])
+                for (int k = 0; k < 8; ++k) {
+                    cudaEventCreateWithFlags(&ev_p[k], cudaEventDisableTiming);
+                    cudaEventCreateWithFlags(&ev_s[k], cudaEventDisableTiming);
+                }
+            if (gmode == 4 && !(b == 0 && g == 0)) CK(cudaStreamWaitEvent(gs, ev_p[(g + ng - 1) % ng], 0));  // no prop || prop
+            if (fast64_propagate(ctx, p, (dir > 0) ? l0 : l1 - 1, l1 - l0, dir, vfirst, 3, gs)) return DQMCB_ECUDA;
+            if (gmode == 4) CK(cudaEventRecord(ev_p[g], gs));
+            if (gmode == 3 && !(b == 0 && g == 0)) CK(cudaStreamWaitEvent(gs, ev_s[(g + ng - 1) % ng], 0));  // no stab || stab
+            if (dbg) {
+                const cudaError_t e = cudaStreamSynchronize(ctx->gstream[g]);
+                if (e != cudaSuccess) {
+                    fprintf(stderr, "[dqmcb debug] propagate failed: %s dir=%d block=%d group=%d w=[%d,%d) mode=%d\n", cudaGetErrorString(e), dir, i, g,
+                            p.w0, p.w1, p.rng_mode);
+                    return DQMCB_ECUDA;
+                }
+            }
+            fast_stabilize(ctx, (dir > 0) ? l1 - 1 : l0, dir, p.w0, p.w1, gs);
+            if (gmode == 1) CK(cudaEventRecord(ctx->gdone[g], gs));
+            if (gmode == 3) CK(cudaEventRecord(ev_s[g], gs));
+            if (dbg) {
+                const cudaError_t e = cudaStreamSynchronize(ctx->gstream[g]);
+                if (e != cudaSuccess) {
+                    fprintf(stderr, "[dqmcb debug] stabilize failed: %s dir=%d block=%d group=%d w=[%d,%d)\n", cudaGetErrorString(e), dir, i, g, p.w0,
+                            p.w1);
+                    return DQMCB_ECUDA;
+                }
+            }
             ctx->n_launches += 2;
         }
     }

@@ -298,10 +298,14 @@ __device__ void qrp_tile(double* __restrict__ A, double* __restrict__ tau, int* 
             if (lane == 0) {
                 tau[j] = t;
                 jpvt[j] = bi;
-                norm2[bi] = -1.0;
             }
         }
         __syncthreads();
+        // retire the pivot column only now: every warp derives the pivot of this step from norm2 on its own, so
+        // the entry must not change before all of them have passed the barrier above (a warp held up for a few
+        // hundred cycles -- e.g. by a co-resident CTA in a tensor-core phase -- would otherwise see the column
+        // already retired, elect a different pivot and run a second, conflicting reflector generation)
+        if (owner && (bi >> 3) == warp && lane == 0) norm2[bi] = -1.0;
         if (owner && done != 0xffu) {
             const double t = tau[j];
             const double vA = vfull[rA], vB = HB ? vfull[rB] : 0.0;

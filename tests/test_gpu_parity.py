@@ -307,3 +307,39 @@ def test_delayed_updates_with_tiles_in_global_memory_and_shared_sms():
     assert rel_err(out[1][1], out[0][1]) < 1e-8
     assert np.array_equal(out[0][2][0], out[1][2][0])
     assert out[1][2][1].max() < 1e-6
+
+
+def test_walker_groups_with_offset_phases_under_host_contention(monkeypatch):
+    """Regression test for a race in the fast-path QR (every warp derives the step's pivot from the shared norm
+    array on its own; the owner used to retire the column before the step's barrier).  It only fired when a
+    warp was held up for a few hundred cycles -- in practice when stabilisation kernels of two walker groups
+    overlapped out of phase, which a busy host makes likely (7 of 8 runs failed with an illegal address).
+    Busy host processes + grouped sweeps must complete and reproduce the single-stream trajectory bit for bit."""
+    import subprocess
+    import sys
+
+    from dqmc_b200 import capi
+
+    cfg = CONFIGS["C1"]
+    W = 1024
+    m, _ = make_oracle(cfg, 5)
+    f0 = np.random.default_rng(12).integers(0, 4, size=(W, cfg[6], 64), dtype=np.int8)
+    burners = [subprocess.Popen([sys.executable, "-c", "import time\nt=time.time()\nwhile time.time()-t<40: pass"]) for _ in range(24)]
+    try:
+        out = []
+        for ng in ("2", "1"):
+            monkeypatch.setenv("DQMCB_STREAMS", ng)
+            ctx = make_ctx(cfg, W, m.expK, m.invexpK)
+            ctx.set_fields(f0)
+            ctx.rng_mode(capi.RNG_PHILOX, 31)
+            ctx.init_stacks()
+            ctx.init_greenfunctions()
+            for s in range(12 if ng == "2" else 12):
+                ctx.sweep_0_to_beta()
+                ctx.sweep_beta_to_0()
+            out.append((ctx.get_fields(), ctx.get_G()))
+            ctx.close()
+    finally:
+        for b in burners:
+            b.kill()
+    assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1])

@@ -144,7 +144,7 @@ def run_reference_arm(args, wl, name):
     from oracle import ref
 
     if not ref.available():
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libdqmc_ref.so was not built (needs /root/reference at build time)"}))
+        emit({"impl": "reference", "unavailable": "oracle/_ref/libdqmc_ref.so was not built (needs /root/reference at build time)"})
         return
     sims = [ref.RefSim(L1, L2, U, t, mu, beta, nt, n_stab, 1000 + i) for i in range(chains)]
     devnull = os.open(os.devnull, os.O_WRONLY)
@@ -174,11 +174,35 @@ def run_reference_arm(args, wl, name):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
+_REAL_STDOUT = None
+
+
+def _quiet_stdout():
+    """Libraries (NCCL prints its version banner on the first communicator) write to fd 1; the contract is ONE
+    JSON line on stdout, so everything else is sent to stderr and the line goes to the saved descriptor."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    _quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
@@ -376,7 +400,7 @@ def main():
         "roofline": roofline,
         "cpu_baseline": cpu_baseline,
     }
-    print(json.dumps(line))
+    emit(line)
     if dist is not None:
         dist.destroy_process_group()
 

@@ -54,6 +54,7 @@ SYMBOLS = [
     "dqmcb_bin_configure", "dqmcb_bin_measure", "dqmcb_bin_fetch", "dqmcb_chi_site_to_chi_r", "dqmcb_chi_r_to_chi_k",
     "dqmcb_pbc_shortest", "dqmcb_sweep_unequal_time", "dqmcb_get_G_unequal", "dqmcb_get_unequal_err",
     "dqmcb_half_wrap_unequal", "dqmcb_measure_unequal_time", "dqmcb_bin_measure_unequal", "dqmcb_bin_fetch_unequal",
+    "dqmcb_set_tape_async", "dqmcb_tape_commit",
 ]
 
 
@@ -190,6 +191,18 @@ class Context:
         u = np.ascontiguousarray(u, dtype=np.float64)
         assert perm.shape == k.shape == u.shape and perm.shape[0] == self.W and perm.shape[2] == self.N
         self._ck(self.L.dqmcb_set_tape(self.h, perm.shape[1], perm.ctypes.data_as(_u8p), k.ctypes.data_as(_u8p), _d(u)))
+
+    def set_tape_async(self, perm, k, u):
+        """Upload the next tape while the current step runs (arrays must be C-contiguous uint8/uint8/float64, ideally
+        views of pinned memory, and stay alive until tape_commit)."""
+        for a, dt in ((perm, np.uint8), (k, np.uint8), (u, np.float64)):
+            assert a.dtype == dt and a.flags["C_CONTIGUOUS"]
+        assert perm.shape == k.shape == u.shape and perm.shape[0] == self.W and perm.shape[2] == self.N
+        self._pending_tape = (perm, k, u)
+        self._ck(self.L.dqmcb_set_tape_async(self.h, perm.shape[1], perm.ctypes.data_as(_u8p), k.ctypes.data_as(_u8p), _d(u)))
+
+    def tape_commit(self):
+        self._ck(self.L.dqmcb_tape_commit(self.h))
 
     # ---- engine ----
     def set_half_expK(self, a, b):

@@ -657,6 +657,12 @@ void dqmcb_destroy(dqmcb_ctx* ctx) {
     cudaFree(p.err_cnt);
     cudaFree(p.fail);
     cudaFree(ctx->d_obs);
+    cudaFree(ctx->d_tape2_perm);
+    cudaFree(ctx->d_tape2_k);
+    cudaFree(ctx->d_tape2_u);
+    if (ctx->cstream) cudaStreamDestroy(ctx->cstream);
+    if (ctx->ev_tape) cudaEventDestroy(ctx->ev_tape);
+    if (ctx->ev_free) cudaEventDestroy(ctx->ev_free);
     cudaFree(ctx->d_binpart);
     cudaFree(ctx->d_binacc);
     cudaFree(ctx->d_uneq);
@@ -814,6 +820,61 @@ int dqmcb_set_tape(dqmcb_ctx* ctx, int n_visits, const uint8_t* perm, const uint
     ctx->p.tape_k = ctx->d_tape_k;
     ctx->p.tape_u = ctx->d_tape_u;
     ctx->p.tape_visits = n_visits;
+    ctx->p.rng_mode = DQMCB_RNG_TAPE;
+    ctx->tape_pos = 0;
+    ctx->p.visit_base = 0;
+    return DQMCB_OK;
+}
+
+// Asynchronous variant for pipelined end-to-end runs: the tape of the NEXT step is uploaded (from pinned host
+// memory, on a copy stream) into the inactive buffer set while the kernels of the current step still read the
+// active one; dqmcb_tape_commit then switches sets in stream order.
+int dqmcb_set_tape_async(dqmcb_ctx* ctx, int n_visits, const uint8_t* perm, const uint8_t* knew, const double* u) {
+    NEED(ctx);
+    if (n_visits <= 0 || !perm || !knew || !u) return DQMCB_EINVAL;
+    const size_t cnt = (size_t)ctx->p.W * n_visits * ctx->p.N;
+    if (!ctx->cstream) {
+        CK(cudaStreamCreateWithFlags(&ctx->cstream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&ctx->ev_tape, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&ctx->ev_free, cudaEventDisableTiming));
+        CK(cudaEventRecord(ctx->ev_free, ctx->stream));
+    }
+    if ((size_t)n_visits > ctx->tape2_cap) {
+        CK(cudaStreamSynchronize(ctx->cstream));
+        cudaFree(ctx->d_tape2_perm);
+        cudaFree(ctx->d_tape2_k);
+        cudaFree(ctx->d_tape2_u);
+        CK(cudaMalloc(&ctx->d_tape2_perm, cnt));
+        CK(cudaMalloc(&ctx->d_tape2_k, cnt));
+        CK(cudaMalloc(&ctx->d_tape2_u, cnt * 8));
+        ctx->tape2_cap = n_visits;
+    }
+    // the inactive set was the active one until the last commit: its readers precede ev_free in ctx->stream
+    CK(cudaStreamWaitEvent(ctx->cstream, ctx->ev_free, 0));
+    CK(cudaMemcpyAsync(ctx->d_tape2_perm, perm, cnt, cudaMemcpyHostToDevice, ctx->cstream));
+    CK(cudaMemcpyAsync(ctx->d_tape2_k, knew, cnt, cudaMemcpyHostToDevice, ctx->cstream));
+    CK(cudaMemcpyAsync(ctx->d_tape2_u, u, cnt * 8, cudaMemcpyHostToDevice, ctx->cstream));
+    CK(cudaEventRecord(ctx->ev_tape, ctx->cstream));
+    ctx->tape2_visits = n_visits;
+    return DQMCB_OK;
+}
+int dqmcb_tape_commit(dqmcb_ctx* ctx) {
+    NEED(ctx);
+    if (ctx->tape2_visits <= 0) {
+        ctx->err = "dqmcb_tape_commit: no tape pending (call dqmcb_set_tape_async first)";
+        return DQMCB_ESTATE;
+    }
+    CK(cudaEventRecord(ctx->ev_free, ctx->stream));           // everything that reads the old set is before this
+    CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_tape, 0));    // the new set is complete before anything after this
+    std::swap(ctx->d_tape_perm, ctx->d_tape2_perm);
+    std::swap(ctx->d_tape_k, ctx->d_tape2_k);
+    std::swap(ctx->d_tape_u, ctx->d_tape2_u);
+    std::swap(ctx->tape_cap, ctx->tape2_cap);
+    ctx->p.tape_perm = ctx->d_tape_perm;
+    ctx->p.tape_k = ctx->d_tape_k;
+    ctx->p.tape_u = ctx->d_tape_u;
+    ctx->p.tape_visits = ctx->tape2_visits;
+    ctx->tape2_visits = 0;
     ctx->p.rng_mode = DQMCB_RNG_TAPE;
     ctx->tape_pos = 0;
     ctx->p.visit_base = 0;

@@ -75,6 +75,14 @@ struct dqmcb_ctx {
     uint8_t *d_tape_perm = nullptr, *d_tape_k = nullptr;
     double* d_tape_u = nullptr;
     size_t tape_cap = 0;  // visits allocated
+    // second tape set + copy stream: dqmcb_set_tape_async uploads the next tape while the sweeps of the current
+    // one run; dqmcb_tape_commit makes it current
+    uint8_t *d_tape2_perm = nullptr, *d_tape2_k = nullptr;
+    double* d_tape2_u = nullptr;
+    size_t tape2_cap = 0;
+    int tape2_visits = 0;          // visits uploaded into the pending set (0 = nothing pending)
+    cudaStream_t cstream = nullptr;
+    cudaEvent_t ev_tape = nullptr, ev_free = nullptr;
     int tape_pos = 0;     // next visit to consume (TAPE mode)
     double* d_obs = nullptr;  // [W][4]
     double* d_scratchNN = nullptr;  // [W][N*N] for measurement outputs

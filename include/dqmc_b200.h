@@ -86,6 +86,10 @@ int dqmcb_rng_seed_mt19937(dqmcb_ctx* ctx, const uint32_t* seeds);
 /* mode TAPE: draws for the next `n_visits` local_update calls of every walker, in visiting order:
  * perm[W][n_visits][N] site order, knew[W][n_visits][N] proposal index 0..2, u[W][n_visits][N]. */
 int dqmcb_set_tape(dqmcb_ctx* ctx, int n_visits, const uint8_t* perm, const uint8_t* knew, const double* u);
+/* Pipelined variant: upload the NEXT tape (pinned host buffers, which must stay valid until the commit) on a copy
+ * stream while the current step's kernels run; dqmcb_tape_commit switches to it in stream order. */
+int dqmcb_set_tape_async(dqmcb_ctx* ctx, int n_visits, const uint8_t* perm, const uint8_t* knew, const double* u);
+int dqmcb_tape_commit(dqmcb_ctx* ctx);
 
 /* ---- stacks and Green's functions (source/dqmc.cpp:43-72) -------------------------------------- */
 int dqmcb_init_stacks(dqmcb_ctx* ctx);         /* DQMC::init_stacks            */

@@ -343,3 +343,40 @@ def test_walker_groups_with_offset_phases_under_host_contention(monkeypatch):
         for b in burners:
             b.kill()
     assert np.array_equal(out[0][0], out[1][0]) and np.array_equal(out[0][1], out[1][1])
+
+
+def test_async_tape_pipeline_equals_synchronous_tape():
+    """dqmcb_set_tape_async + dqmcb_tape_commit (next step's tape uploaded while the current step runs) must give
+    exactly the trajectory of the synchronous dqmcb_set_tape, step after step."""
+    cfg = CONFIGS["C1s"]
+    W, nt, n = 96, cfg[6], 64
+    m, _ = make_oracle(cfg, 5)
+    f0 = np.random.default_rng(2).integers(0, 4, size=(W, nt, n), dtype=np.int8)
+    gen = np.random.default_rng(3)
+    tapes = []
+    for s in range(4):
+        perm = gen.permuted(np.tile(np.arange(n, dtype=np.uint8), (W, 2 * nt, 1)), axis=-1)
+        tapes.append((np.ascontiguousarray(perm), gen.integers(0, 3, size=(W, 2 * nt, n), dtype=np.uint8), gen.random((W, 2 * nt, n))))
+    outs = []
+    for mode in ("sync", "async"):
+        ctx = make_ctx(cfg, W, m.expK, m.invexpK)
+        ctx.set_fields(f0)
+        ctx.init_stacks()
+        ctx.init_greenfunctions()
+        res = []
+        if mode == "async":
+            ctx.set_tape_async(*tapes[0])
+            ctx.tape_commit()
+        for s in range(4):
+            if mode == "sync":
+                ctx.set_tape(*tapes[s])
+            elif s + 1 < 4:
+                ctx.set_tape_async(*tapes[s + 1])
+            f, sc, G = ctx.run_sweeps_host(None, 1, want_G=True)
+            if mode == "async" and s + 1 < 4:
+                ctx.tape_commit()
+            res.append((f, sc, G))
+        outs.append(res)
+        ctx.close()
+    for a, b in zip(*outs):
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and np.array_equal(a[2], b[2])

@@ -184,6 +184,12 @@ class Context:
     def rng_mode(self, mode: int, seed: int = 0):
         self._ck(self.L.dqmcb_rng_mode(self.h, mode, seed))
 
+    def rng_seed_mt19937(self, seeds):
+        """Device-resident std::mt19937(seeds[w]) per walker: the reference's libstdc++ stream, no host tape."""
+        s = np.ascontiguousarray(seeds, dtype=np.uint32)
+        assert s.shape == (self.W,)
+        self._ck(self.L.dqmcb_rng_seed_mt19937(self.h, s.ctypes.data_as(C.POINTER(C.c_uint32))))
+
     def set_tape(self, perm, k, u):
         """perm/k/u: [W, n_visits, N] in visiting order."""
         perm = np.ascontiguousarray(perm, dtype=np.uint8)

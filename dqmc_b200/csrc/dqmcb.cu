@@ -16,6 +16,7 @@
 #include "engine.cuh"
 #include "fast64.cuh"
 #include "measure.cuh"
+#include "mt19937.cuh"
 
 using namespace dq;
 
@@ -780,12 +781,29 @@ int dqmcb_get_fields_i64(dqmcb_ctx* ctx, int walker, long long* f) {
 }
 
 // ---- RNG ----------------------------------------------------------------------------------------------
+static int mt_seed(dqmcb_ctx* ctx, const uint32_t* seeds) {
+    const Params& p = ctx->p;
+    if (!ctx->d_mt) CK(cudaMalloc(&ctx->d_mt, (size_t)p.W * 625 * sizeof(uint32_t)));
+    uint32_t* d_seeds = nullptr;
+    CK(cudaMalloc(&d_seeds, (size_t)p.W * sizeof(uint32_t)));
+    CK(cudaMemcpy(d_seeds, seeds, (size_t)p.W * sizeof(uint32_t), cudaMemcpyHostToDevice));
+    k_mt_seed<<<(p.W + 127) / 128, 128, 0, ctx->stream>>>(p.W, d_seeds, ctx->d_mt);
+    CK(cudaGetLastError());
+    CK(cudaStreamSynchronize(ctx->stream));
+    cudaFree(d_seeds);
+    ctx->p.rng_mode = DQMCB_RNG_MT19937;
+    ctx->p.visit_base = 0;
+    ctx->tape_pos = 0;
+    ctx->p.tape_visits = 0;
+    return DQMCB_OK;
+}
 int dqmcb_rng_mode(dqmcb_ctx* ctx, int mode, uint64_t seed) {
-    if (!ctx) return DQMCB_EINVAL;
+    NEED(ctx);
     if (mode != DQMCB_RNG_TAPE && mode != DQMCB_RNG_PHILOX && mode != DQMCB_RNG_MT19937) return DQMCB_EINVAL;
-    if (mode == DQMCB_RNG_MT19937) {
-        ctx->err = "device mt19937 stream not built in this version: replay it through DQMCB_RNG_TAPE";
-        return DQMCB_EINVAL;
+    if (mode == DQMCB_RNG_MT19937) {  // walker w gets std::mt19937(seed + w)
+        std::vector<uint32_t> seeds(ctx->p.W);
+        for (int w = 0; w < ctx->p.W; ++w) seeds[w] = (uint32_t)(seed + (uint64_t)w);
+        return mt_seed(ctx, seeds.data());
     }
     ctx->p.rng_mode = mode;
     ctx->p.seed = seed;
@@ -794,10 +812,42 @@ int dqmcb_rng_mode(dqmcb_ctx* ctx, int mode, uint64_t seed) {
     ctx->p.tape_visits = 0;
     return DQMCB_OK;
 }
-int dqmcb_rng_seed_mt19937(dqmcb_ctx* ctx, const uint32_t*) {
-    if (!ctx) return DQMCB_EINVAL;
-    ctx->err = "device mt19937 stream not built in this version: replay it through DQMCB_RNG_TAPE";
-    return DQMCB_EINVAL;
+int dqmcb_rng_seed_mt19937(dqmcb_ctx* ctx, const uint32_t* seeds) {
+    NEED(ctx);
+    if (!seeds) return DQMCB_EINVAL;
+    return mt_seed(ctx, seeds);
+}
+// MT19937 mode: regenerate the next `n` visits of every walker's libstdc++ stream into the tape buffers
+static int mt_refill(dqmcb_ctx* ctx, int n) {
+    const Params& p = ctx->p;
+    const size_t cnt = (size_t)p.W * n * p.N;
+    if ((size_t)n > ctx->tape_cap) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        cudaFree(ctx->d_tape_perm);
+        cudaFree(ctx->d_tape_k);
+        cudaFree(ctx->d_tape_u);
+        CK(cudaMalloc(&ctx->d_tape_perm, cnt));
+        CK(cudaMalloc(&ctx->d_tape_k, cnt));
+        CK(cudaMalloc(&ctx->d_tape_u, cnt * 8));
+        ctx->tape_cap = n;
+    }
+    const size_t smem = (size_t)624 * kMtWalkers * sizeof(uint32_t) + (size_t)p.N * kMtWalkers;
+    static bool attr_set = false;
+    if (!attr_set) {
+        CK(cudaFuncSetAttribute(k_mt_fill, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(624 * kMtWalkers * 4 + 256 * kMtWalkers)));
+        attr_set = true;
+    }
+    k_mt_fill<<<(p.W + kMtWalkers - 1) / kMtWalkers, kMtWalkers, smem, ctx->stream>>>(p.W, p.N, n, ctx->d_mt, ctx->d_tape_perm, ctx->d_tape_k,
+                                                                                     ctx->d_tape_u);
+    CK(cudaGetLastError());
+    ctx->n_launches += 1;
+    ctx->p.tape_perm = ctx->d_tape_perm;
+    ctx->p.tape_k = ctx->d_tape_k;
+    ctx->p.tape_u = ctx->d_tape_u;
+    ctx->p.tape_visits = n;
+    ctx->tape_pos = 0;
+    ctx->p.visit_base = 0;
+    return DQMCB_OK;
 }
 int dqmcb_set_tape(dqmcb_ctx* ctx, int n_visits, const uint8_t* perm, const uint8_t* knew, const double* u) {
     NEED(ctx);
@@ -883,6 +933,12 @@ int dqmcb_tape_commit(dqmcb_ctx* ctx) {
 
 // consume `n` visits: returns the first visit index to hand to the kernel
 static int take_visits(dqmcb_ctx* ctx, int n, unsigned long long* first) {
+    if (ctx->p.rng_mode == DQMCB_RNG_MT19937) {  // the stream is consumed strictly in call order: generate exactly n visits
+        if (int rc = mt_refill(ctx, n)) return rc;
+        *first = 0;
+        ctx->tape_pos = n;
+        return DQMCB_OK;
+    }
     if (ctx->p.rng_mode == DQMCB_RNG_TAPE) {
         if (ctx->tape_pos + n > ctx->p.tape_visits) {
             ctx->err = "RNG tape exhausted: call dqmcb_set_tape with enough visits";

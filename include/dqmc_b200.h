@@ -81,7 +81,9 @@ int dqmcb_get_fields_i64(dqmcb_ctx* ctx, int walker, long long* fields);
 
 /* ---- RNG ---------------------------------------------------------------------------------------- */
 int dqmcb_rng_mode(dqmcb_ctx* ctx, int mode, uint64_t seed);
-/* mode MT19937: one std::mt19937 seed per walker (utility::random ctor, include/utility.h:27) */
+/* mode MT19937: one std::mt19937 seed per walker (utility::random ctor, include/utility.h:27); selects the mode.
+ * dqmcb_rng_mode(ctx, DQMCB_RNG_MT19937, seed) seeds walker w with seed + w.  The stream is consumed in call
+ * order exactly as the reference consumes it (N/2 + 2N words per local_update for even N). */
 int dqmcb_rng_seed_mt19937(dqmcb_ctx* ctx, const uint32_t* seeds);
 /* mode TAPE: draws for the next `n_visits` local_update calls of every walker, in visiting order:
  * perm[W][n_visits][N] site order, knew[W][n_visits][N] proposal index 0..2, u[W][n_visits][N]. */

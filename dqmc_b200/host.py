@@ -71,6 +71,19 @@ class AttractiveHubbard:
         return f
 
 
+def reference_fields(seed: int, nt: int, n_sites: int) -> np.ndarray:
+    """The random start of the reference for `utility::random rng(seed)`: GHQField's constructor
+    (include/field.h:52-57) fills the column-major nt x N matrix with uniform_int_distribution<int>(0, 3) drawn
+    from a COPY of the generator (the stream of the sweeps then starts again at the seeded state).  For a 32-bit
+    engine and a range of 4 libstdc++'s multiply-shift never rejects, so each value is the top two bits of one
+    mt19937 word.  Returns int8 fields[l, site]."""
+    bg = np.random.MT19937()
+    bg._legacy_seeding(int(seed) & 0xFFFFFFFF)  # init_genrand(seed) = std::mt19937(seed)
+    words = bg.random_raw(nt * n_sites).astype(np.uint64)
+    flat = (words >> np.uint64(30)).astype(np.int8)
+    return np.ascontiguousarray(flat.reshape(n_sites, nt).T)
+
+
 class DQMC:
     """Batched counterpart of `class DQMC` (include/dqmc.h:21): sweeps over all walkers of a model."""
 

@@ -11,8 +11,10 @@ sweep_0_to_beta, sweep_beta_to_0, sweep_unequalTime (if isMeasureUnequalTime), m
 results/data_<rank>.h5 (HDF5 is not available here) and rank 0 writes `<out>/info` (include/lattice.h:110-136).
 
 Differences from the reference, all additive: W walkers per rank instead of one chain (every measure() adds W
-samples to the bin); Philox counter-based random numbers (the libstdc++-exact stream lives in the C++ mirror,
-include/dqmcb/dqmc.h); checkpoint/resume of fields, bins and counters (absent in the reference; a resumed run
+samples to the bin); Philox counter-based random numbers by default -- `--rng mt19937` regenerates the
+reference's libstdc++ stream on the device instead, walker w of rank r = utility::random(seed + r*W + w) with the
+reference's random start, so that `--walkers 1 --rng mt19937 --seed S` writes the bins the reference program
+writes for rng(S) (tests/golden/program.npz); checkpoint/resume of fields, bins and counters (absent in the reference; a resumed run
 continues with a fresh random stream: statistically equivalent, not bit-identical).  `symmetric` is read and
 ignored exactly as the reference's measurements ignore the half-warped copy (source/main.cpp:161-165 measures
 `greens`, not `greens_symm`).
@@ -46,6 +48,9 @@ def main(argv=None) -> dict:
     ap.add_argument("--out", default="results")
     ap.add_argument("--checkpoint-every", type=int, default=0, help="bins between checkpoints (0 = off)")
     ap.add_argument("--resume", action="store_true")
+    ap.add_argument("--rng", default="philox", choices=["philox", "mt19937"],
+                    help="mt19937: walker w of rank r runs the reference's libstdc++ stream of utility::random(seed + r*W + w), "
+                         "random start included -- a --walkers 1 run then reproduces the reference program's bins")
     ap.add_argument("--delay-k", type=int, default=-1, help="delayed rank-k updates (default: 32 for N >= 128, else off)")
     args = ap.parse_args(argv)
 
@@ -91,9 +96,16 @@ def main(argv=None) -> dict:
         mm.current_bin = start_bin
         mm.datasets = {k[3:]: z[k] for k in z.files if k.startswith("ds:")}
         seed += 7919 * (start_bin + 1)  # fresh stream after a restart
+    elif args.rng == "mt19937":
+        base = (int(time.time()) if args.seed is None else args.seed) + rank * args.walkers
+        ctx.set_fields(np.stack([host.reference_fields(base + w, nt, N) for w in range(args.walkers)]))
     else:
         model.random_fields(seed)       # GHQField's random start (include/field.h:52-57), one draw per walker
-    ctx.rng_mode(capi.RNG_PHILOX, seed)
+    if args.rng == "mt19937":
+        base = (int(time.time()) if args.seed is None else args.seed) + rank * args.walkers + (7919 * start_bin if therm_done else 0)
+        ctx.rng_seed_mt19937(np.arange(base, base + args.walkers, dtype=np.uint64).astype(np.uint32))
+    else:
+        ctx.rng_mode(capi.RNG_PHILOX, seed)
     ctx.init_stacks()
     ctx.init_greenfunctions()
     ex = None
@@ -106,8 +118,8 @@ def main(argv=None) -> dict:
         save_info(os.path.join(args.out, "info"), L1, L2)
         print(f"{'Parallel Tempering enabled.' if pt else 'Standard DQMC run (Parallel Tempering disabled).'}", flush=True)
 
-    def one_sweep(isweep: int) -> None:
-        if ex is not None and isweep % exchange_step == 0:
+    def one_sweep(isweep: int, exchange: bool = True) -> None:
+        if exchange and ex is not None and isweep % exchange_step == 0:
             dist.barrier()
             ex.step()
         ctx.sweep_0_to_beta()
@@ -115,12 +127,12 @@ def main(argv=None) -> dict:
 
     t0 = time.perf_counter()
     if not therm_done:
-        for isweep in range(1, n_therms + 1):  # source/main.cpp:126-137
-            one_sweep(isweep)
+        for isweep in range(1, n_therms + 1):  # source/main.cpp:130-133: no exchange while thermalising
+            one_sweep(isweep, exchange=False)
         ctx.synchronize()
     t_therm = time.perf_counter() - t0
     t0 = time.perf_counter()
-    for b in range(start_bin, n_bins):          # source/main.cpp:139-171
+    for b in range(start_bin, n_bins):          # source/main.cpp:145-171
         for s in range(1, n_sweeps + 1):
             one_sweep(b * n_sweeps + s)
             if unequal:

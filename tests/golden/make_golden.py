@@ -253,6 +253,42 @@ def unequal_case():
     np.savez_compressed(os.path.join(HERE, "unequal.npz"), **out)
 
 
+PROGRAM_CFG = dict(L1=4, L2=4, U=4.0, t=1.0, mu=-0.1, beta=1.0, nt=10, n_stab=5, seed=11, n_therms=3, n_sweeps=2, n_bins=3)
+
+
+def program_case():
+    """The whole program: the loop of source/main.cpp:126-171 (thermalise, then per sweep sweep_0_to_beta,
+    sweep_beta_to_0, sweep_unequalTime, measure; accumulate per bin) run by the reference's own classes for
+    utility::random rng(seed), isMeasureUnequalTime = true.  The datasets of results/data_0.h5 are the fixture
+    `python -m dqmc_b200.run --rng mt19937 --walkers 1 --seed 11` must reproduce (tests/test_gpu_driver.py)."""
+    c = PROGRAM_CFG
+    nt = c["nt"]
+    s = ref.RefSim(c["L1"], c["L2"], c["U"], c["t"], c["mu"], c["beta"], nt, c["n_stab"], c["seed"], unequal=True)
+    mm = ref.RefMeasure(c["L1"], c["L2"], rank=0, unequal=True)
+    out = {"cfg_keys": np.array(list(c.keys())), "cfg": np.array(list(c.values()), dtype=np.float64),
+           "fields0": s.fields().astype(np.int8)}
+    tok = silence_stderr()
+    try:
+        for _ in range(c["n_therms"]):
+            s.sweep_fwd()
+            s.sweep_bwd()
+        for isweep in range(1, c["n_bins"] * c["n_sweeps"] + 1):
+            s.sweep_fwd()
+            s.sweep_bwd()
+            s.sweep_unequal()
+            mm.measure_unequal(*[np.stack([s.G_unequal(wh, l) for l in range(nt + 1)]) for wh in range(3)])
+            if isweep % c["n_sweeps"] == 0:
+                mm.accumulate()
+    finally:
+        restore_stderr(tok)
+    out["fields"] = s.fields().astype(np.int8)
+    out["acc_rate"] = np.array(s.acc_rate())
+    for k, v in mm.datasets().items():
+        out["ds:" + k] = v
+    mm.close()
+    np.savez_compressed(os.path.join(HERE, "program.npz"), **out)
+
+
 if __name__ == "__main__":
     assert ref.build(), "oracle/_ref could not be built (needs /root/reference)"
     for nm, cfg in CASES.items():
@@ -262,4 +298,5 @@ if __name__ == "__main__":
     exchange_case()
     measure_case()
     unequal_case()
+    program_case()
     print("golden fixtures written to", HERE)

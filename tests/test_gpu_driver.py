@@ -34,11 +34,11 @@ betas = 5.0, 4.5
 """
 
 
-def _run(tmp_path, *extra):
+def _run(tmp_path, *extra, walkers=8):
     pf = tmp_path / "parameters.in"
     pf.write_text(PARAMS)
     out = tmp_path / "results"
-    r = subprocess.run([sys.executable, "-m", "dqmc_b200.run", str(pf), "--walkers", "8", "--seed", "11", "--out", str(out), *extra],
+    r = subprocess.run([sys.executable, "-m", "dqmc_b200.run", str(pf), "--walkers", str(walkers), "--seed", "11", "--out", str(out), *extra],
                        capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert r.returncode == 0, r.stderr
     return out, json.loads(r.stdout.strip().splitlines()[-1]), r.stdout
@@ -83,3 +83,29 @@ def test_driver_checkpoint_and_resume(tmp_path):
         if "/bin_2/" not in k and "/binK_2/" not in k:
             assert np.array_equal(z[k], keep[k]), k
     assert s2["thermalisation_s"] < 1e-3  # no second thermalisation
+
+
+def test_driver_mt19937_reproduces_the_reference_program(tmp_path):
+    """`--rng mt19937 --walkers 1 --seed 11`: the whole program of source/main.cpp (random start from a copy of
+    rng(11), 3 thermalisation sweeps, 3 bins of 2 sweeps with sweep_unequalTime + measure, accumulate) must write
+    the datasets the reference's own DQMC + MeasurementManager classes recorded for the same parameter file
+    (tests/golden/program.npz, made by tests/golden/make_golden.py:program_case).  No host random numbers: the
+    libstdc++ stream is regenerated on the device.  Walker 1 of a 2-walker run is rng(12): its chain differs, and
+    the bins are then the mean of two chains."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "program.npz"))
+    c = dict(zip([str(k) for k in g["cfg_keys"]], g["cfg"]))
+    assert (c["L1"], c["nt"], c["n_therms"], c["n_sweeps"], c["n_bins"], c["seed"]) == (4, 10, 3, 2, 3, 11)
+    out, summary, _ = _run(tmp_path, "--rng", "mt19937", walkers=1)
+    with np.load(out / "data_0.npz") as f:
+        z = {k: f[k] for k in f.files}
+    paths = sorted(k[3:] for k in g.files if k.startswith("ds:"))
+    assert sorted(z) == paths
+    for p in paths:
+        want, got = g["ds:" + p], z[p]
+        assert got.shape == want.shape, p
+        tol = 1e-10 if "/scalar/" in p or "/equaltime/" in p else 1e-7  # tau > 0 goes through naive propagation on both sides
+        assert np.max(np.abs(got - want)) <= tol * max(1.0, np.max(np.abs(want))), p
+    assert abs(summary["acceptance_rate"] - float(g["acc_rate"]) / 18.0) < 1e-12  # 2 * (3 + 6) half sweeps
+    out2, s2, _ = _run(tmp_path, "--rng", "mt19937", walkers=2)
+    z2 = np.load(out2 / "data_0.npz")
+    assert abs(z2["/bin_0/scalar/doubleOcc"][0] - z["/bin_0/scalar/doubleOcc"][0]) > 1e-6

@@ -351,3 +351,44 @@ def test_measurement_manager_unequal_golden():
         want = g["a_ds:" + p]
         assert mm.datasets[p].shape == want.shape, p
         assert rel(mm.datasets[p], want) < 1e-12, p
+
+
+def test_whole_program_golden():
+    """The loop of source/main.cpp:126-171 in the oracle (mt19937 stream, random start, thermalisation, bins with
+    unequal-time on) against the datasets the reference's own classes recorded for rng(11) (tests/golden/program.npz)."""
+    g = load("program.npz")
+    c = dict(zip([str(k) for k in g["cfg_keys"]], g["cfg"]))
+    L1, L2, nt, n_stab, seed = int(c["L1"]), int(c["L2"]), int(c["nt"]), int(c["n_stab"]), int(c["seed"])
+    n = L1 * L2
+    f0 = O.random_fields(seed, nt, n)
+    assert np.array_equal(f0, g["fields0"])
+    m = O.Model(L1, L2, c["U"], c["t"], c["mu"], c["beta"], nt, fields=f0)
+    d = O.DQMC(m, n_stab)
+    d.init_stacks()
+    d.init_greenfunctions()
+    gen = O.MT19937(seed)
+    mm = O.MeasurementManager(L1, L2, unequal=True)
+
+    def sweep():
+        tape = O.rng_tape(gen, n, 2 * nt)
+        d.sweep_0_to_beta((tape[0][:nt], tape[1][:nt], tape[2][:nt]))
+        d.sweep_beta_to_0((tape[0][nt:], tape[1][nt:], tape[2][nt:]))
+
+    for _ in range(int(c["n_therms"])):
+        sweep()
+    for isweep in range(1, int(c["n_bins"] * c["n_sweeps"]) + 1):
+        sweep()
+        d.sweep_unequalTime()
+        mm.measure_unequal(d.Gtt_all, d.Gt0_all, d.G0t_all)
+        if isweep % int(c["n_sweeps"]) == 0:
+            mm.accumulate()
+    assert np.array_equal(m.fields, g["fields"])
+    paths = sorted(k[3:] for k in g.files if k.startswith("ds:"))
+    assert paths == sorted(mm.datasets) and len(paths) == 3 * 11
+    for p in paths:
+        assert mm.datasets[p].shape == g["ds:" + p].shape, p
+        assert rel(mm.datasets[p], g["ds:" + p]) < 1e-7, p
+    for b in range(3):
+        for s in ("density", "doubleOcc", "swave"):
+            p = f"/bin_{b}/scalar/{s}"
+            assert rel(mm.datasets[p], g["ds:" + p]) < 1e-10, p

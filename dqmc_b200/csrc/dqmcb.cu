@@ -686,9 +686,12 @@ void dqmcb_destroy(dqmcb_ctx* ctx) {
         cudaDeviceSynchronize();
         if (cudaMemcpy(h, p.prof, sizeof(h), cudaMemcpyDeviceToHost) == cudaSuccess) {
             fprintf(stderr, "[dqmcb phase prof] clock64 offsets from stamp 0, last instrumented launch (CTA 0):");
-            for (int i = 1; i < 64; ++i)
+            for (int i = 1; i < 40; ++i)
                 if (h[i]) fprintf(stderr, " %d:%lld", i, h[i] - h[0]);
             fprintf(stderr, "\n");
+            if (h[44])  // accumulated over every kf_propagate launch, walker 0 of CTA 0
+                fprintf(stderr, "[dqmcb phase prof] propagate (walker 0, per slice): wrap %lld clk, Metropolis %lld clk, draws+rest %lld clk, accepts %.1f of N\n",
+                        h[40] / h[44], h[41] / h[44], (h[43] - h[40] - h[41]) / h[44], (double)h[42] / (double)h[44]);
         }
         cudaFree(p.prof);
     }

@@ -397,12 +397,17 @@ __device__ void form_q_tile(double* __restrict__ Q, const double* __restrict__ V
 // records the row chosen at step j, and the final store writes row perm[i] to position i, which
 // yields exactly dgetrf's in-place layout (unit-lower multipliers below the diagonal, U on and above
 // it) -- same pivots, same multipliers, same arithmetic as the interchanging form.
-// ONE block barrier per step: the warp owning column j finds the pivot among the still-active rows
-// (integer REDUX argmax), publishes the multiplier column through a double-buffered shared vector,
-// and every warp applies the rank-1 update to its own register columns; the pivot-row values are
-// fetched with one shuffle per column.
+//
+// PANEL form: the warp owning columns [8 pb, 8 pb + 8) factorises its whole panel on its own -- pivot
+// search (integer REDUX argmax), reciprocal, multipliers and the rank-1 updates of its remaining panel
+// columns need warp-level exchange only -- and publishes the eight multiplier columns and pivot rows
+// through a double-buffered shared panel; ONE block barrier per panel (N/8 per factorisation instead of
+// N), after which every warp to the right applies the eight rank-1 updates to its own register columns
+// in step order (so every element sees the same operations in the same order as the column-at-a-time
+// form).  The panel buffer lives in the storage of tile A itself, which is dead between the initial
+// load and the final store.
 // Outputs: factors in A (dgetrf layout), perm[i] = original row at position i, rdiag[j] = 1/U(j,j),
-// ipiv is not produced (the solve uses perm).  lbuf: 2 N doubles of scratch.
+// ipiv is not produced (the solve uses perm).  lbuf: >= 16 ints of scratch (pivot rows of two panels).
 // ------------------------------------------------------------------------------------------------
 template <int N>
 __device__ void lu_tile(double* __restrict__ A, int* __restrict__ perm, double* __restrict__ rdiag, int* __restrict__ info,
@@ -410,10 +415,12 @@ __device__ void lu_tile(double* __restrict__ A, int* __restrict__ perm, double* 
     static_assert(N == 32 || N == 64, "lu_tile: one warp per 8-column block, two rows per lane");
     constexpr int LDT = Tile<N>::LDT;
     constexpr bool HB = N > 32;
+    static_assert(2 * 8 * N <= Tile<N>::ELEMS, "panel buffers must fit in the tile");
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int rA = lane, rB = lane + 32;
     const int cbase = 8 * warp;
     const bool owner = cbase < N;
+    int* pvbuf = reinterpret_cast<int*>(lbuf);
     double ca[8], cb[8];
     bool actA = true, actB = HB;  // my rows not yet chosen as pivot rows
     int posA = 0, posB = 0;       // step at which my rows were chosen = their final position
@@ -426,57 +433,79 @@ __device__ void lu_tile(double* __restrict__ A, int* __restrict__ perm, double* 
             cb[q] = HB ? cp[rB] : 0.0;
         }
     }
-    __syncthreads();  // everybody has read A; *info initialised
-    for (int j = 0; j < N; ++j) {
-        double* lb = lbuf + (j & 1) * (N + 2);  // [0..N-1] multipliers, [N] pivot row (as double)
-        if (owner && (j >> 3) == warp) {
-            const int qs = j & 7;
-            double x = 0.0, y = 0.0;
+    __syncthreads();  // everybody has read A (its storage now carries the panels); *info initialised
+    for (int pb = 0; pb < N / 8; ++pb) {
+        double* Lp = A + (size_t)(pb & 1) * 8 * N;  // [jj][row] multipliers of step 8 pb + jj
+        int* pv = pvbuf + (pb & 1) * 8;             // pivot row of step 8 pb + jj
+        if (warp == pb) {
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                x = (q == qs) ? ca[q] : x;
-                y = (q == qs) ? cb[q] : y;
-            }
-            const int p = warp_argmax2(fabs(x), rA, actA, fabs(y), rB, actB);
-            const double piv = __shfl_sync(DQ_FULL, (p < 32) ? x : y, p & 31);
-            const double rinv = (piv != 0.0) ? 1.0 / piv : 0.0;
-            // multipliers of the rows that stay active; they are also the L entries of column j
-            const double lA = (actA && rA != p) ? x * rinv : 0.0;
-            const double lB = (actB && rB != p) ? y * rinv : 0.0;
-            lb[rA] = lA;
-            if (HB) lb[rB] = lB;
-            if (actA && rA != p) x = lA;
-            if (actB && rB != p) y = lB;
+            for (int jj = 0; jj < 8; ++jj) {
+                const int j = 8 * pb + jj;
+                const double x = ca[jj], y = cb[jj];
+                const int p = warp_argmax2(fabs(x), rA, actA, fabs(y), rB, actB);
+                const double piv = __shfl_sync(DQ_FULL, (p < 32) ? x : y, p & 31);
+                const double rinv = (piv != 0.0) ? 1.0 / piv : 0.0;
+                // multipliers of the rows that stay active; they are also the L entries of column j
+                const bool kA = actA && rA != p, kB = actB && rB != p;
+                const double lA = kA ? x * rinv : 0.0;
+                const double lB = kB ? y * rinv : 0.0;
+                Lp[jj * N + rA] = lA;
+                if (HB) Lp[jj * N + rB] = lB;
+                if (kA) ca[jj] = lA;
+                if (kB) cb[jj] = lB;
+                if (rA == p) {
+                    actA = false;
+                    posA = j;
+                }
+                if (rB == p) {
+                    actB = false;
+                    posB = j;
+                }
+                if (lane == 0) {
+                    pv[jj] = p;
+                    perm[j] = p;
+                    rdiag[j] = rinv;
+                    if (piv == 0.0 && *info == 0) *info = j + 1;
+                }
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                ca[q] = (q == qs) ? x : ca[q];
-                cb[q] = (q == qs) ? y : cb[q];
-            }
-            if (lane == 0) {
-                lb[N] = (double)p;
-                perm[j] = p;
-                rdiag[j] = rinv;
-                if (piv == 0.0 && *info == 0) *info = j + 1;
+                for (int q = jj + 1; q < 8; ++q) {
+                    const double u = __shfl_sync(DQ_FULL, (p < 32) ? ca[q] : cb[q], p & 31);
+                    ca[q] = fma(-lA, u, ca[q]);
+                    cb[q] = fma(-lB, u, cb[q]);
+                }
             }
         }
         __syncthreads();
-        const int p = (int)lb[N];
-        if (rA == p) {
-            actA = false;
-            posA = j;
-        }
-        if (rB == p) {
-            actB = false;
-            posB = j;
-        }
-        if (owner && cbase + 7 > j) {
-            const double lA = lb[rA], lB = HB ? lb[rB] : 0.0;  // zero for frozen rows and for row p
+        if (warp != pb) {
+            int pj[8];
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                const double u = __shfl_sync(DQ_FULL, (p < 32) ? ca[q] : cb[q], p & 31);
-                if (cbase + q > j) {
-                    ca[q] = fma(-lA, u, ca[q]);
-                    cb[q] = fma(-lB, u, cb[q]);
+            for (int jj = 0; jj < 8; ++jj) {
+                pj[jj] = pv[jj];
+                if (rA == pj[jj]) {
+                    actA = false;
+                    posA = 8 * pb + jj;
+                }
+                if (rB == pj[jj]) {
+                    actB = false;
+                    posB = 8 * pb + jj;
+                }
+            }
+            if (owner && warp > pb) {
+                double lA[8], lB[8];  // zero for rows frozen before the step and for its pivot row
+#pragma unroll
+                for (int jj = 0; jj < 8; ++jj) {
+                    lA[jj] = Lp[jj * N + rA];
+                    lB[jj] = HB ? Lp[jj * N + rB] : 0.0;
+                }
+#pragma unroll
+                for (int jj = 0; jj < 8; ++jj) {
+                    const int p = pj[jj];
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        const double u = __shfl_sync(DQ_FULL, (p < 32) ? ca[q] : cb[q], p & 31);
+                        ca[q] = fma(-lA[jj], u, ca[q]);
+                        cb[q] = fma(-lB[jj], u, cb[q]);
+                    }
                 }
             }
         }
@@ -494,50 +523,125 @@ __device__ void lu_tile(double* __restrict__ A, int* __restrict__ perm, double* 
     __syncthreads();
 }
 
-// dgetrs 'N' in place on an N x N right-hand side: element (i, c) at Bm[i*rsB + c*csB].
-// Two adjacent lanes own one right-hand-side column (even / odd rows, N/2 values each in registers;
-// threads 0..2N-1, i.e. four warps for N = 64).  The triangular factors are read as warp-wide
-// broadcasts; the only exchange per elimination step is one shuffle between the two lanes of a
-// column.  Uses perm / rdiag from lu_tile.  Caller synchronises before and after.
+// dgetrs 'N' in place on an N x N right-hand side: element (i, c) at Bm[i*rsB + c*csB].  BLOCKED by
+// 8 rows: the 8 x 8 diagonal block is solved in registers, one thread per right-hand-side column
+// (seven dependent FMAs), and the remaining block rows are updated with rank-8 FP64 tensor-core
+// products (two DMMA.8x8x4 per 8 x 8 block, the warp's B fragment loaded once per block row);
+// two block barriers per block row -- 4 N / 8 per solve instead of a 2 N step serial chain.
+// Uses perm / rdiag from lu_tile.  All threads of the CTA must call; caller synchronises before and after.
 template <int N>
 __device__ __noinline__ void lu_solve_tile(const double* __restrict__ A, const int* __restrict__ perm, const double* __restrict__ rdiag,
                                            double* __restrict__ Bm, int rsB, int csB) {
-    static_assert(N % 2 == 0 && N <= 64, "lu_solve_tile layout");
+    static_assert(N == 32 || N == 64, "lu_solve_tile layout");
     constexpr int LDT = Tile<N>::LDT;
-    constexpr int H = N / 2;
-    const int t = threadIdx.x;
-    if (t >= 2 * N) return;  // whole warps only (2N is a multiple of 32 for N = 32, 64)
-    const int c = t >> 1, h = t & 1, lane = t & 31;
-    const int pair = lane & ~1;
-    double x[H];  // x[m] = row 2m + h
-    double* col = Bm + (size_t)c * csB;
+    constexpr int NBK = N / 8;
+    const int t = threadIdx.x, nthr = blockDim.x;
+    const int lane = t & 31, warp = t >> 5, nwarps = nthr >> 5, gr = lane >> 2, tg = lane & 3;
+    // ---- b <- P b: every element is read before any is written.  The unit-stride index of the
+    // right-hand side runs across the lanes (fast), eight entries of the other index per thread.
+    {
+        constexpr int NPARTS = kThreads / N;
+        constexpr int PASSES = (N + NPARTS * 8 - 1) / (NPARTS * 8);
+        const int f = t % N, part = t / N;
+        const bool rows_fast = (rsB == 1);
+        double v[PASSES][8];
 #pragma unroll
-    for (int m = 0; m < H; ++m) x[m] = col[(size_t)perm[2 * m + h] * rsB];
-    // forward: L y = P b (unit diagonal)
+        for (int ps = 0; ps < PASSES; ++ps) {
+            const int s0 = (ps * NPARTS + part) * 8;
+            if (s0 < N) {
 #pragma unroll
-    for (int k = 0; k < N - 1; ++k) {
-        const double xk = __shfl_sync(DQ_FULL, x[k >> 1], pair | (k & 1));
-        const double* lk = A + (size_t)k * LDT + h;
-        if ((k & 1) == 0) {
-            if (h) x[k >> 1] = fma(-lk[k], xk, x[k >> 1]);  // row k+1 (odd lane)
+                for (int i = 0; i < 8; ++i)
+                    v[ps][i] = rows_fast ? Bm[(size_t)perm[f] + (size_t)(s0 + i) * csB] : Bm[(size_t)perm[s0 + i] * rsB + (size_t)f];
+            }
         }
+        __syncthreads();
 #pragma unroll
-        for (int m = (k >> 1) + 1; m < H; ++m) x[m] = fma(-lk[2 * m], xk, x[m]);
-    }
-    // backward: U x = y
+        for (int ps = 0; ps < PASSES; ++ps) {
+            const int s0 = (ps * NPARTS + part) * 8;
+            if (s0 < N) {
 #pragma unroll
-    for (int k = N - 1; k >= 0; --k) {
-        const double xk = __shfl_sync(DQ_FULL, x[k >> 1] * rdiag[k], pair | (k & 1));
-        if (h == (k & 1)) x[k >> 1] = xk;
-        const double* uk = A + (size_t)k * LDT + h;
-#pragma unroll
-        for (int m = 0; m < (k >> 1); ++m) x[m] = fma(-uk[2 * m], xk, x[m]);
-        if (k & 1) {
-            if (!h) x[k >> 1] = fma(-uk[k - 1], xk, x[k >> 1]);  // row k-1 (even lane)
+                for (int i = 0; i < 8; ++i) {
+                    if (rows_fast)
+                        Bm[(size_t)f + (size_t)(s0 + i) * csB] = v[ps][i];
+                    else
+                        Bm[(size_t)(s0 + i) * rsB + (size_t)f] = v[ps][i];
+                }
+            }
         }
+        __syncthreads();
     }
+    // ---- forward: L y = P b (unit diagonal)
+    for (int kb = 0; kb < NBK; ++kb) {
+        const int k0 = 8 * kb;
+        if (t < N) {
+            double* col = Bm + (size_t)k0 * rsB + (size_t)t * csB;
+            double x[8];
 #pragma unroll
-    for (int m = 0; m < H; ++m) col[(size_t)(2 * m + h) * rsB] = x[m];
+            for (int i = 0; i < 8; ++i) x[i] = col[(size_t)i * rsB];
+#pragma unroll
+            for (int j = 0; j < 7; ++j) {
+                const double* lj = A + k0 + (size_t)(k0 + j) * LDT;
+#pragma unroll
+                for (int i = j + 1; i < 8; ++i) x[i] = fma(-lj[i], x[j], x[i]);
+            }
+#pragma unroll
+            for (int i = 1; i < 8; ++i) col[(size_t)i * rsB] = x[i];
+        }
+        if (kb + 1 == NBK) break;
+        __syncthreads();
+        const int ntask = (NBK - 1 - kb) * NBK;
+        for (int task = warp; task < ntask; task += nwarps) {
+            const int cb = task % NBK, rb = kb + 1 + task / NBK;
+            const double* ap = A + (8 * rb + gr) + (size_t)(k0 + tg) * LDT;
+            const double* bp = Bm + (size_t)(k0 + tg) * rsB + (size_t)(8 * cb + gr) * csB;
+            double* cp = Bm + (size_t)(8 * rb + gr) * rsB + (size_t)(8 * cb + 2 * tg) * csB;
+            const double a0 = -ap[0], a1 = -ap[4 * LDT];
+            const double b0 = bp[0], b1 = bp[(size_t)4 * rsB];
+            double c0 = cp[0], c1 = cp[csB];
+            dmma884(c0, c1, a0, b0);
+            dmma884(c0, c1, a1, b1);
+            cp[0] = c0;
+            cp[csB] = c1;
+        }
+        __syncthreads();
+    }
+    __syncthreads();
+    // ---- backward: U x = y
+    for (int kb = NBK - 1; kb >= 0; --kb) {
+        const int k0 = 8 * kb;
+        if (t < N) {
+            double* col = Bm + (size_t)k0 * rsB + (size_t)t * csB;
+            double x[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) x[i] = col[(size_t)i * rsB];
+#pragma unroll
+            for (int j = 7; j >= 0; --j) {
+                const double* uj = A + k0 + (size_t)(k0 + j) * LDT;
+                x[j] *= rdiag[k0 + j];
+#pragma unroll
+                for (int i = 0; i < j; ++i) x[i] = fma(-uj[i], x[j], x[i]);
+            }
+#pragma unroll
+            for (int i = 0; i < 8; ++i) col[(size_t)i * rsB] = x[i];
+        }
+        if (kb == 0) break;
+        __syncthreads();
+        const int ntask = kb * NBK;
+        for (int task = warp; task < ntask; task += nwarps) {
+            const int cb = task % NBK, rb = task / NBK;
+            const double* ap = A + (8 * rb + gr) + (size_t)(k0 + tg) * LDT;
+            const double* bp = Bm + (size_t)(k0 + tg) * rsB + (size_t)(8 * cb + gr) * csB;
+            double* cp = Bm + (size_t)(8 * rb + gr) * rsB + (size_t)(8 * cb + 2 * tg) * csB;
+            const double a0 = -ap[0], a1 = -ap[4 * LDT];
+            const double b0 = bp[0], b1 = bp[(size_t)4 * rsB];
+            double c0 = cp[0], c1 = cp[csB];
+            dmma884(c0, c1, a0, b0);
+            dmma884(c0, c1, a1, b1);
+            cp[0] = c0;
+            cp[csB] = c1;
+        }
+        __syncthreads();
+    }
 }
 
 }  // namespace dq

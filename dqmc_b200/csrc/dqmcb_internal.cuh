@@ -59,7 +59,9 @@ struct Params {
 // phase stamp k of CTA 0 / thread 0 (no-op unless the context was created with DQMCB_PHASE_PROF=1)
 #define DQ_PH(p, k)                                                                         \
     do {                                                                                    \
+        asm volatile("" ::: "memory");                                                      \
         if ((p).prof && blockIdx.x == 0 && threadIdx.x == 0) (p).prof[k] = clock64();       \
+        asm volatile("" ::: "memory");                                                      \
     } while (0)
 
 }  // namespace dq

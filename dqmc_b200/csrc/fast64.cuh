@@ -77,7 +77,7 @@ __device__ void f_to_ldr(const Params& p, FWork<N>& wk, double* A, double* Qo, d
     constexpr int LDT = Tile<N>::LDT;
     __syncthreads();
     DQ_PH(p, 20);
-    qrp_tile<N>(A, wk.tau, wk.jpvt, wk.vn1, wk.sv[1], wk.sv[3]);
+    qrp_tile<N>(A, wk.tau, wk.jpvt, wk.vn1, wk.sv[1], wk.sv[3], wk.vn2);
     DQ_PH(p, 21);
     // column jpvt[j] of A holds R(0..j, j) (and the reflector below): d_j = |R(j,j)|, and
     // R_final = (D^-1 R) P^T puts that column back at index jpvt[j] -- where it already is
@@ -252,6 +252,19 @@ __global__ void __launch_bounds__(kThreads, 2) kf_stabilize(Params p, int l, int
     fcarve<N>(wk, smem);
     const int i = l / p.n_stab;
     DQ_PH(p, 0);
+    // The two neighbouring stack entries (the one the new entry is built from and the one it is combined
+    // with for G) stream from HBM: pull them into L2 now, behind the Bbar chain and the QR.
+    if (threadIdx.x == 0) {
+        constexpr uint32_t MB_ = (uint32_t)(N * N * sizeof(double));
+        if (i > 0) {
+            bulk_prefetch_l2(fstkL(p, w, i - 1), MB_);
+            bulk_prefetch_l2(fstkR(p, w, i - 1), MB_);
+        }
+        if (i + 1 < p.n_stack) {
+            bulk_prefetch_l2(fstkL(p, w, i + 1), MB_);
+            bulk_prefetch_l2(fstkR(p, w, i + 1), MB_);
+        }
+    }
     f_bbar<N>(p, wk, w, i);  // -> t[0]
     double *t0 = wk.t[0], *t1 = wk.t[1], *t2 = wk.t[2];
     __syncthreads();
@@ -268,10 +281,16 @@ __global__ void __launch_bounds__(kThreads, 2) kf_stabilize(Params p, int l, int
         __syncthreads();
         cta_mma<N, false>(t2, LDT, t0, 1, LDT, t1, 1, LDT, nullptr, wk.sv[0]);
         f_to_ldr<N>(p, wk, t2, t0, t1, wk.dnew);
+        fence_proxy_async();
+        tile_load_async<N>(t2, fstkR(p, w, i - 1), wk.bar);  // in flight while L is written out
+        DQ_PH(p, 24);
         tile_store_global<N>(fstkL(p, w, i), t0);
-        tile_fetch<N>(wk, t2, fstkR(p, w, i - 1));
+        mbar_wait(wk.bar, wk.parity);
+        wk.parity ^= 1;
         __syncthreads();
+        DQ_PH(p, 25);
         cta_mma<N, false>(fstkR(p, w, i), N, t1, 1, LDT, t2, 1, LDT, nullptr, nullptr);
+        DQ_PH(p, 26);
     } else {
         // ldr_mul_mat: D_next (R_next Bbar) -> QR ; L <- L_next Q
         fstore_d(wk.sv[0], fstkD(p, w, i + 1), N);
@@ -279,8 +298,11 @@ __global__ void __launch_bounds__(kThreads, 2) kf_stabilize(Params p, int l, int
         __syncthreads();
         cta_mma<N, false>(t2, LDT, t1, 1, LDT, t0, 1, LDT, wk.sv[0], nullptr);
         f_to_ldr<N>(p, wk, t2, t0, t1, wk.dnew);
+        fence_proxy_async();
+        tile_load_async<N>(t2, fstkL(p, w, i + 1), wk.bar);  // in flight while R is written out
         tile_store_global<N>(fstkR(p, w, i), t1);
-        tile_fetch<N>(wk, t2, fstkL(p, w, i + 1));
+        mbar_wait(wk.bar, wk.parity);
+        wk.parity ^= 1;
         __syncthreads();
         cta_mma<N, false>(fstkL(p, w, i), N, t2, 1, LDT, t0, 1, LDT, nullptr, nullptr);
     }

@@ -173,6 +173,11 @@ __device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gsrc, uint3
                  "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// TMA bulk prefetch of `bytes` (multiple of 16) of global memory into L2 (SASS UBLKPF): issued by one thread
+// long before a matrix is needed, so that the later fetch / operand loads hit L2 instead of HBM.
+__device__ __forceinline__ void bulk_prefetch_l2(const void* gsrc, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;\n" ::"l"(gsrc), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
 
 // Issue the copy of an N x N global matrix (ld = N, 16-byte aligned) into tile `dst` (ld = LDT).
@@ -231,12 +236,14 @@ __device__ __forceinline__ void tile_load_global(double* __restrict__ tile, cons
 //   * two block barriers per step; the reflector application needs no shared-memory traffic for the
 //     matrix and reduces the eight dot products of a warp with one transposing butterfly
 //     (9 shuffles instead of 40).
-// norm2[N]: squared partial norms (-1 = column already chosen); vfull[N]: dense reflector;
-// wbuf[N]: tau * (v^T a_c).
+//   * the owner of the elected column publishes it RAW; beta, tau and the scaling of the reflector are derived
+//     from it by every warp on its own, so that sqrt / divisions overlap the dot-product reductions.
+// norm2[N]: squared partial norms (-1 = column already chosen); xraw[N]: raw pivot column;
+// wbuf[N]: tau * (v^T a_c); ajbuf[N]: row j of the trailing matrix.
 // ------------------------------------------------------------------------------------------------
 template <int N>
 __device__ void qrp_tile(double* __restrict__ A, double* __restrict__ tau, int* __restrict__ jpvt, double* __restrict__ norm2,
-                         double* __restrict__ vfull, double* __restrict__ wbuf) {
+                         double* __restrict__ xraw, double* __restrict__ wbuf, double* __restrict__ ajbuf) {
     static_assert(N == 32 || N == 64, "qrp_tile: one warp per 8-column block, two rows per lane");
     constexpr int LDT = Tile<N>::LDT;
     constexpr bool HB = N > 32;
@@ -264,57 +271,59 @@ __device__ void qrp_tile(double* __restrict__ A, double* __restrict__ tau, int* 
         // ---- pivot (every warp computes it: no barrier needed to publish it)
         const int pc1 = lane + 32;
         const double n0 = norm2[lane], n1 = HB ? norm2[pc1] : -1.0;
-        const int bi = warp_argmax2(n0, lane, n0 >= 0.0, n1, pc1, HB && n1 >= 0.0);
-        if (owner && (bi >> 3) == warp) {
-            // ---- dlarfg on rows j.. of the pivot column
-            const int qs = bi & 7;
+        const int bi = warp_argmax2_64(n0, lane, n0 >= 0.0, n1, pc1, HB && n1 >= 0.0);
+        const double n2 = norm2[bi];  // exact |a(j:, bi)|^2 (recomputed after the previous reflector)
+        const bool piv_owner = owner && (bi >> 3) == warp;
+        const int qs = bi & 7;
+        if (piv_owner) {
+            // publish the RAW pivot column; the reflector scalars are derived from it by every warp on
+            // its own, overlapped with the dot products, instead of serially by this warp
             double x = 0.0, y = 0.0;
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
                 x = (q == qs) ? ca[q] : x;
                 y = (q == qs) ? cb[q] : y;
             }
-            const double alpha = __shfl_sync(DQ_FULL, (j < 32) ? x : y, j & 31);
-            const double xs = (rA > j) ? x : 0.0, ys = (HB && rB > j) ? y : 0.0;
-            const double xn2 = warp_sum(fma(xs, xs, ys * ys));
-            double t = 0.0;
-            if (xn2 != 0.0) {
-                const double beta = -copysign(sqrt(fma(alpha, alpha, xn2)), alpha);
-                t = (beta - alpha) / beta;
-                const double scal = 1.0 / (alpha - beta);
-                if (rA > j) x *= scal;
-                if (rB > j) y *= scal;
-                if (rA == j) x = beta;
-                if (rB == j) y = beta;
-            }
-#pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                ca[q] = (q == qs) ? x : ca[q];
-                cb[q] = (q == qs) ? y : cb[q];
-            }
-            done |= 1u << qs;
-            vfull[rA] = (rA > j) ? x : ((rA == j) ? 1.0 : 0.0);
-            if (HB) vfull[rB] = (rB > j) ? y : ((rB == j) ? 1.0 : 0.0);
-            if (lane == 0) {
-                tau[j] = t;
-                jpvt[j] = bi;
-            }
+            xraw[rA] = x;
+            if (HB) xraw[rB] = y;
+            if (lane == 0) jpvt[j] = bi;
         }
         __syncthreads();
         // retire the pivot column only now: every warp derives the pivot of this step from norm2 on its own, so
         // the entry must not change before all of them have passed the barrier above (a warp held up for a few
         // hundred cycles -- e.g. by a co-resident CTA in a tensor-core phase -- would otherwise see the column
-        // already retired, elect a different pivot and run a second, conflicting reflector generation)
-        if (owner && (bi >> 3) == warp && lane == 0) norm2[bi] = -1.0;
-        if (owner && done != 0xffu) {
-            const double t = tau[j];
-            const double vA = vfull[rA], vB = HB ? vfull[rB] : 0.0;
+        // already retired and elect a different pivot)
+        if (piv_owner && lane == 0) norm2[bi] = -1.0;
+        if (piv_owner) done |= 1u << qs;
+        if (owner && (done != 0xffu || piv_owner)) {
+            const double xA = xraw[rA], xB = HB ? xraw[rB] : 0.0;
+            const double alpha = xraw[j];
+            // ---- dlarfg scalars (all lanes, redundantly; a latency chain that overlaps the reductions below):
+            // beta = -sign(alpha) |a(j:)|, tau = (beta - alpha) / beta, v = x / (alpha - beta) below the diagonal.
+            // |a(j:)|^2 is the exact partial norm the column was elected with; H = I if nothing is below.
+            const bool below = (rA > j && xA != 0.0) || (HB && rB > j && xB != 0.0);
+            const bool refl = __any_sync(DQ_FULL, below);
+            // With beta = -sign(alpha) nrm:  tau = 1 + |alpha| / nrm,  1 / (alpha - beta) = sign(alpha) / (|alpha| + nrm).
+            double hrs;
+            const double nrm = sqrt_newton(refl ? fmax(n2, alpha * alpha) : 1.0, &hrs);
+            const double beta = refl ? -copysign(nrm, alpha) : alpha;
+            const double t = refl ? fma(fabs(alpha), hrs + hrs, 1.0) : 0.0;
+            const double scal = refl ? copysign(rcp_newton(fabs(alpha) + nrm), alpha) : 0.0;
+            // ---- raw dot products x(j+1:)^T a_c and the row-j entries a(j, c)
+            const double mA = (rA > j) ? xA : 0.0, mB = (HB && rB > j) ? xB : 0.0;
             double pr[8];
 #pragma unroll
-            for (int q = 0; q < 8; ++q) pr[q] = fma(vA, ca[q], vB * cb[q]);
-            const double tot = warp_sum8_transposed(pr);
-            if ((lane & 3) == 0) wbuf[cbase + mycol] = t * tot;
+            for (int q = 0; q < 8; ++q) pr[q] = fma(mA, ca[q], mB * cb[q]);
+            if (lane == (j & 31)) {
+#pragma unroll
+                for (int q = 0; q < 8; ++q) ajbuf[cbase + q] = (j < 32) ? ca[q] : cb[q];
+            }
+            const double raw = warp_sum8_transposed(pr);
             __syncwarp();
+            if ((lane & 3) == 0) wbuf[cbase + mycol] = t * fma(scal, raw, ajbuf[cbase + mycol]);  // tau (v^T a_c)
+            __syncwarp();
+            const double vA = (rA > j) ? xA * scal : ((rA == j) ? 1.0 : 0.0);
+            const double vB = (HB && rB > j) ? xB * scal : ((rB == j) ? 1.0 : 0.0);
             double s[8];
 #pragma unroll
             for (int q = 0; q < 8; ++q) {
@@ -324,8 +333,19 @@ __device__ void qrp_tile(double* __restrict__ A, double* __restrict__ tau, int* 
                 const double ea = (rA > j) ? ca[q] : 0.0, eb = (HB && rB > j) ? cb[q] : 0.0;
                 s[q] = fma(ea, ea, eb * eb);
             }
-            const double n2 = warp_sum8_transposed(s);  // exact |a(j+1:, c)|^2
-            if ((lane & 3) == 0 && !((done >> mycol) & 1u)) norm2[cbase + mycol] = n2;
+            if (piv_owner) {
+                // the pivot column becomes (R(0..j-1, j), beta, v(j+1:))
+                const double x = (rA > j) ? vA : ((rA == j) ? beta : xA);
+                const double y = (rB > j) ? vB : ((rB == j) ? beta : xB);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    ca[q] = (q == qs) ? x : ca[q];
+                    cb[q] = (q == qs) ? y : cb[q];
+                }
+                if (lane == 0) tau[j] = t;
+            }
+            const double nn = warp_sum8_transposed(s);  // exact |a(j+1:, c)|^2
+            if ((lane & 3) == 0 && !((done >> mycol) & 1u)) norm2[cbase + mycol] = nn;
         }
         __syncthreads();
     }
@@ -442,9 +462,9 @@ __device__ void lu_tile(double* __restrict__ A, int* __restrict__ perm, double* 
             for (int jj = 0; jj < 8; ++jj) {
                 const int j = 8 * pb + jj;
                 const double x = ca[jj], y = cb[jj];
-                const int p = warp_argmax2(fabs(x), rA, actA, fabs(y), rB, actB);
+                const int p = warp_argmax2_64(fabs(x), rA, actA, fabs(y), rB, actB);
                 const double piv = __shfl_sync(DQ_FULL, (p < 32) ? x : y, p & 31);
-                const double rinv = (piv != 0.0) ? 1.0 / piv : 0.0;
+                const double rinv = (piv != 0.0) ? rcp_newton(piv) : 0.0;
                 // multipliers of the rows that stay active; they are also the L entries of column j
                 const bool kA = actA && rA != p, kB = actB && rB != p;
                 const double lA = kA ? x * rinv : 0.0;
@@ -523,124 +543,101 @@ __device__ void lu_tile(double* __restrict__ A, int* __restrict__ perm, double* 
     __syncthreads();
 }
 
-// dgetrs 'N' in place on an N x N right-hand side: element (i, c) at Bm[i*rsB + c*csB].  BLOCKED by
-// 8 rows: the 8 x 8 diagonal block is solved in registers, one thread per right-hand-side column
-// (seven dependent FMAs), and the remaining block rows are updated with rank-8 FP64 tensor-core
-// products (two DMMA.8x8x4 per 8 x 8 block, the warp's B fragment loaded once per block row);
-// two block barriers per block row -- 4 N / 8 per solve instead of a 2 N step serial chain.
-// Uses perm / rdiag from lu_tile.  All threads of the CTA must call; caller synchronises before and after.
+// dgetrs 'N' in place on an N x N right-hand side: element (i, c) at Bm[i*rsB + c*csB].
+//
+// The N right-hand-side columns are independent, so warp q solves the columns [8q, 8q+8) completely on
+// its own -- NO block barrier, no shared-memory traffic for the right-hand side: the warp's 64 x 8 block
+// lives in registers in the FP64 tensor-core accumulator layout (row block rb: lane (gr, tg) holds rows
+// 8 rb + gr, columns 2 tg, 2 tg + 1).  Per 8-row block: the 8 x 8 triangular system is solved by
+// substitution across the lanes (one shuffle + one FMA per row step), the solved block is turned into a
+// DMMA B fragment with four shuffles, and every remaining row block gets its rank-8 update as two
+// DMMA.8x8x4 straight on the register accumulators (A fragments = blocks of L / U from the shared tile).
+// Backward substitution keeps the unscaled values on the dependent chain (U entries pre-multiplied by the
+// reciprocal pivots, which does not depend on the data).  Uses perm / rdiag from lu_tile.  All threads
+// of the CTA may call; the caller synchronises before and after.
 template <int N>
 __device__ __noinline__ void lu_solve_tile(const double* __restrict__ A, const int* __restrict__ perm, const double* __restrict__ rdiag,
                                            double* __restrict__ Bm, int rsB, int csB) {
     static_assert(N == 32 || N == 64, "lu_solve_tile layout");
     constexpr int LDT = Tile<N>::LDT;
     constexpr int NBK = N / 8;
-    const int t = threadIdx.x, nthr = blockDim.x;
-    const int lane = t & 31, warp = t >> 5, nwarps = nthr >> 5, gr = lane >> 2, tg = lane & 3;
-    // ---- b <- P b: every element is read before any is written.  The unit-stride index of the
-    // right-hand side runs across the lanes (fast), eight entries of the other index per thread.
-    {
-        constexpr int NPARTS = kThreads / N;
-        constexpr int PASSES = (N + NPARTS * 8 - 1) / (NPARTS * 8);
-        const int f = t % N, part = t / N;
-        const bool rows_fast = (rsB == 1);
-        double v[PASSES][8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, gr = lane >> 2, tg = lane & 3;
+    if (8 * warp >= N) return;  // whole warps only
+    double* bcol = Bm + (size_t)(8 * warp + 2 * tg) * csB;
+    double c[NBK][2];
+    // ---- b <- P b while loading (the warp reads and writes only its own columns)
 #pragma unroll
-        for (int ps = 0; ps < PASSES; ++ps) {
-            const int s0 = (ps * NPARTS + part) * 8;
-            if (s0 < N) {
-#pragma unroll
-                for (int i = 0; i < 8; ++i)
-                    v[ps][i] = rows_fast ? Bm[(size_t)perm[f] + (size_t)(s0 + i) * csB] : Bm[(size_t)perm[s0 + i] * rsB + (size_t)f];
-            }
-        }
-        __syncthreads();
-#pragma unroll
-        for (int ps = 0; ps < PASSES; ++ps) {
-            const int s0 = (ps * NPARTS + part) * 8;
-            if (s0 < N) {
-#pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    if (rows_fast)
-                        Bm[(size_t)f + (size_t)(s0 + i) * csB] = v[ps][i];
-                    else
-                        Bm[(size_t)(s0 + i) * rsB + (size_t)f] = v[ps][i];
-                }
-            }
-        }
-        __syncthreads();
+    for (int rb = 0; rb < NBK; ++rb) {
+        const size_t ro = (size_t)perm[8 * rb + gr] * rsB;
+        c[rb][0] = bcol[ro];
+        c[rb][1] = bcol[ro + csB];
     }
+    const int src0 = (tg << 2) | (gr >> 1), src1 = ((tg + 4) << 2) | (gr >> 1);
+    const bool odd = gr & 1;
     // ---- forward: L y = P b (unit diagonal)
+#pragma unroll
     for (int kb = 0; kb < NBK; ++kb) {
         const int k0 = 8 * kb;
-        if (t < N) {
-            double* col = Bm + (size_t)k0 * rsB + (size_t)t * csB;
-            double x[8];
+        double l[7];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) x[i] = col[(size_t)i * rsB];
+        for (int jj = 0; jj < 7; ++jj) l[jj] = A[(k0 + gr) + (size_t)(k0 + jj) * LDT];  // row gr of the diagonal block
 #pragma unroll
-            for (int j = 0; j < 7; ++j) {
-                const double* lj = A + k0 + (size_t)(k0 + j) * LDT;
-#pragma unroll
-                for (int i = j + 1; i < 8; ++i) x[i] = fma(-lj[i], x[j], x[i]);
+        for (int jj = 0; jj < 7; ++jj) {
+            const double v0 = __shfl_sync(DQ_FULL, c[kb][0], (jj << 2) | tg);
+            const double v1 = __shfl_sync(DQ_FULL, c[kb][1], (jj << 2) | tg);
+            if (gr > jj) {
+                c[kb][0] = fma(-l[jj], v0, c[kb][0]);
+                c[kb][1] = fma(-l[jj], v1, c[kb][1]);
             }
+        }
+        if (kb + 1 < NBK) {
+            const double e00 = __shfl_sync(DQ_FULL, c[kb][0], src0), e01 = __shfl_sync(DQ_FULL, c[kb][1], src0);
+            const double e10 = __shfl_sync(DQ_FULL, c[kb][0], src1), e11 = __shfl_sync(DQ_FULL, c[kb][1], src1);
+            const double b0 = odd ? e01 : e00, b1 = odd ? e11 : e10;
 #pragma unroll
-            for (int i = 1; i < 8; ++i) col[(size_t)i * rsB] = x[i];
+            for (int rb = kb + 1; rb < NBK; ++rb) {
+                const double* ap = A + (8 * rb + gr) + (size_t)(k0 + tg) * LDT;
+                dmma884(c[rb][0], c[rb][1], -ap[0], b0);
+                dmma884(c[rb][0], c[rb][1], -ap[4 * LDT], b1);
+            }
         }
-        if (kb + 1 == NBK) break;
-        __syncthreads();
-        const int ntask = (NBK - 1 - kb) * NBK;
-        for (int task = warp; task < ntask; task += nwarps) {
-            const int cb = task % NBK, rb = kb + 1 + task / NBK;
-            const double* ap = A + (8 * rb + gr) + (size_t)(k0 + tg) * LDT;
-            const double* bp = Bm + (size_t)(k0 + tg) * rsB + (size_t)(8 * cb + gr) * csB;
-            double* cp = Bm + (size_t)(8 * rb + gr) * rsB + (size_t)(8 * cb + 2 * tg) * csB;
-            const double a0 = -ap[0], a1 = -ap[4 * LDT];
-            const double b0 = bp[0], b1 = bp[(size_t)4 * rsB];
-            double c0 = cp[0], c1 = cp[csB];
-            dmma884(c0, c1, a0, b0);
-            dmma884(c0, c1, a1, b1);
-            cp[0] = c0;
-            cp[csB] = c1;
-        }
-        __syncthreads();
     }
-    __syncthreads();
     // ---- backward: U x = y
+#pragma unroll
     for (int kb = NBK - 1; kb >= 0; --kb) {
         const int k0 = 8 * kb;
-        if (t < N) {
-            double* col = Bm + (size_t)k0 * rsB + (size_t)t * csB;
-            double x[8];
+        const double rd = rdiag[k0 + gr];
+        double u[8];
 #pragma unroll
-            for (int i = 0; i < 8; ++i) x[i] = col[(size_t)i * rsB];
+        for (int jj = 1; jj < 8; ++jj) u[jj] = A[(k0 + gr) + (size_t)(k0 + jj) * LDT] * rdiag[k0 + jj];  // U(gr, jj) / U(jj, jj)
 #pragma unroll
-            for (int j = 7; j >= 0; --j) {
-                const double* uj = A + k0 + (size_t)(k0 + j) * LDT;
-                x[j] *= rdiag[k0 + j];
-#pragma unroll
-                for (int i = 0; i < j; ++i) x[i] = fma(-uj[i], x[j], x[i]);
+        for (int jj = 7; jj >= 1; --jj) {
+            const double v0 = __shfl_sync(DQ_FULL, c[kb][0], (jj << 2) | tg);  // y_jj before its division by the pivot
+            const double v1 = __shfl_sync(DQ_FULL, c[kb][1], (jj << 2) | tg);
+            if (gr < jj) {
+                c[kb][0] = fma(-u[jj], v0, c[kb][0]);
+                c[kb][1] = fma(-u[jj], v1, c[kb][1]);
             }
+        }
+        c[kb][0] *= rd;
+        c[kb][1] *= rd;
+        if (kb > 0) {
+            const double e00 = __shfl_sync(DQ_FULL, c[kb][0], src0), e01 = __shfl_sync(DQ_FULL, c[kb][1], src0);
+            const double e10 = __shfl_sync(DQ_FULL, c[kb][0], src1), e11 = __shfl_sync(DQ_FULL, c[kb][1], src1);
+            const double b0 = odd ? e01 : e00, b1 = odd ? e11 : e10;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) col[(size_t)i * rsB] = x[i];
+            for (int rb = 0; rb < kb; ++rb) {
+                const double* ap = A + (8 * rb + gr) + (size_t)(k0 + tg) * LDT;
+                dmma884(c[rb][0], c[rb][1], -ap[0], b0);
+                dmma884(c[rb][0], c[rb][1], -ap[4 * LDT], b1);
+            }
         }
-        if (kb == 0) break;
-        __syncthreads();
-        const int ntask = kb * NBK;
-        for (int task = warp; task < ntask; task += nwarps) {
-            const int cb = task % NBK, rb = task / NBK;
-            const double* ap = A + (8 * rb + gr) + (size_t)(k0 + tg) * LDT;
-            const double* bp = Bm + (size_t)(k0 + tg) * rsB + (size_t)(8 * cb + gr) * csB;
-            double* cp = Bm + (size_t)(8 * rb + gr) * rsB + (size_t)(8 * cb + 2 * tg) * csB;
-            const double a0 = -ap[0], a1 = -ap[4 * LDT];
-            const double b0 = bp[0], b1 = bp[(size_t)4 * rsB];
-            double c0 = cp[0], c1 = cp[csB];
-            dmma884(c0, c1, a0, b0);
-            dmma884(c0, c1, a1, b1);
-            cp[0] = c0;
-            cp[csB] = c1;
-        }
-        __syncthreads();
+    }
+#pragma unroll
+    for (int rb = 0; rb < NBK; ++rb) {
+        const size_t ro = (size_t)(8 * rb + gr) * rsB;
+        bcol[ro] = c[rb][0];
+        bcol[ro + csB] = c[rb][1];
     }
 }
 

@@ -77,7 +77,7 @@ __device__ void f_to_ldr(const Params& p, FWork<N>& wk, double* A, double* Qo, d
     constexpr int LDT = Tile<N>::LDT;
     __syncthreads();
     DQ_PH(p, 20);
-    qrp_tile<N>(A, wk.tau, wk.jpvt, wk.vn1, wk.sv[1], wk.sv[3], wk.vn2);
+    qrp_tile<N>(A, wk.tau, wk.jpvt, wk.vn1, wk.sv[1]);  // sv[1..2] (contiguous, dead here): the published pivot column
     DQ_PH(p, 21);
     // column jpvt[j] of A holds R(0..j, j) (and the reflector below): d_j = |R(j,j)|, and
     // R_final = (D^-1 R) P^T puts that column back at index jpvt[j] -- where it already is

@@ -222,8 +222,11 @@ __device__ __forceinline__ void tile_load_global(double* __restrict__ tile, cons
 }
 
 // ------------------------------------------------------------------------------------------------
-// Column-pivoted Householder QR, compile-time N in {32, 64}, REGISTER resident: warp q owns the
-// columns [8q, 8q+8) for the whole factorisation (lane = rows lane, lane+32: 16 doubles per lane).
+// Column-pivoted Householder QR, compile-time N in {32, 64}, REGISTER resident.
+//
+// Layout: TPC = 256 / N adjacent lanes own one column (RPT = N / TPC consecutive rows each: 16 doubles
+// per thread for N = 64), so a column dot product is RPT thread-local FMAs plus log2(TPC) shuffle
+// stages, and the whole CTA works on all N columns at once.
 //
 //   * pivoting is implicit: columns never move; jpvt[j] = the column chosen at step j (LAPACK's
 //     jpvt) and a chosen column is frozen.  On exit column jpvt[j] of A holds R(0..j, j) in rows
@@ -231,131 +234,158 @@ __device__ __forceinline__ void tile_load_global(double* __restrict__ tile, cons
 //   * pivot rule: largest partial column norm |a(j:, c)|, as in dgeqp3/dlaqp2.  LAPACK tracks these
 //     norms by down-dating and recomputes them exactly whenever cancellation threatens (which, on
 //     the strongly graded matrices of the stabilisation, is most of the time); here they are simply
-//     recomputed exactly every step (one extra transposing reduction), so no safeguard logic
-//     exists.  The pivot order can differ from LAPACK's only on floating-point near-ties.
-//   * two block barriers per step; the reflector application needs no shared-memory traffic for the
-//     matrix and reduces the eight dot products of a warp with one transposing butterfly
-//     (9 shuffles instead of 40).
-//   * the owner of the elected column publishes it RAW; beta, tau and the scaling of the reflector are derived
-//     from it by every warp on its own, so that sqrt / divisions overlap the dot-product reductions.
-// norm2[N]: squared partial norms (-1 = column already chosen); xraw[N]: raw pivot column;
-// wbuf[N]: tau * (v^T a_c); ajbuf[N]: row j of the trailing matrix.
+//     recomputed exactly every step, so no safeguard logic exists.  The pivot order can differ from
+//     LAPACK's only on floating-point near-ties.
+//   * a finished row is RETIRED: at step j the entry R(j, c) of every trailing column goes straight to
+//     its place in the shared tile (whose storage is dead while the matrix lives in registers) and the
+//     register is zeroed.  Registers therefore hold exact zeros in rows <= j, and neither the dot
+//     products nor the norms nor the published pivot column need row masks.  The step loop is unrolled
+//     over the RPT rows of a thread, so "row j" is a compile-time register index.
+//   * the owners of the elected column publish it RAW; beta, tau and the scaling of the reflector are
+//     derived from it by every thread on its own (branch-free sqrt / reciprocal), overlapping the dot
+//     products.  The weight tau (v^T a_c) is computed redundantly by the TPC lanes of a column: no
+//     shared-memory exchange besides the pivot column.  Two block barriers per step.
+// norm2[N]: squared partial norms (-1 = column already chosen); xraw[(RPT + 2) TPC]: raw pivot column,
+// chunk of RPT rows per lane-of-column padded to RPT + 2 (conflict-free 16-byte loads).
 // ------------------------------------------------------------------------------------------------
 template <int N>
 __device__ void qrp_tile(double* __restrict__ A, double* __restrict__ tau, int* __restrict__ jpvt, double* __restrict__ norm2,
-                         double* __restrict__ xraw, double* __restrict__ wbuf, double* __restrict__ ajbuf) {
-    static_assert(N == 32 || N == 64, "qrp_tile: one warp per 8-column block, two rows per lane");
+                         double* __restrict__ xraw) {
+    static_assert(N == 32 || N == 64, "qrp_tile: 256 threads, 256 / N lanes per column");
     constexpr int LDT = Tile<N>::LDT;
     constexpr bool HB = N > 32;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int rA = lane, rB = lane + 32;
-    const int cbase = 8 * warp;
-    const bool owner = cbase < N;
-    const int mycol = ((lane >> 4) & 1) * 4 + ((lane >> 3) & 1) * 2 + ((lane >> 2) & 1);  // see warp_sum8_transposed
-    double ca[8], cb[8];
-    unsigned done = 0;  // bit q: column cbase + q already chosen
-    if (owner) {
-        double s[8];
+    constexpr int TPC = kThreads / N;  // lanes per column
+    constexpr int RPT = N / TPC;       // rows per lane
+    constexpr int XS = RPT + 2;        // padded chunk stride of the published column
+    static_assert(RPT % 2 == 0, "16-byte loads of the published column");
+    const int lane = threadIdx.x & 31;
+    const int c = threadIdx.x / TPC, sub = threadIdx.x % TPC;
+    const int grp = lane & ~(TPC - 1);
+    const unsigned gmask = ((1u << TPC) - 1u) << grp;
+    double a[RPT];
+    {
+        const double* cp = A + (size_t)c * LDT + sub * RPT;
+        double s0 = 0.0, s1 = 0.0;
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            const double* cp = A + (size_t)(cbase + q) * LDT;
-            ca[q] = cp[rA];
-            cb[q] = HB ? cp[rB] : 0.0;
-            s[q] = fma(ca[q], ca[q], cb[q] * cb[q]);
+        for (int k = 0; k < RPT; k += 2) {
+            const double2 v = *reinterpret_cast<const double2*>(cp + k);
+            a[k] = v.x;
+            a[k + 1] = v.y;
+            s0 = fma(v.x, v.x, s0);
+            s1 = fma(v.y, v.y, s1);
         }
-        const double tot = warp_sum8_transposed(s);
-        if ((lane & 3) == 0) norm2[cbase + mycol] = tot;
+        double sq = s0 + s1;
+#pragma unroll
+        for (int o = 1; o < TPC; o <<= 1) sq += __shfl_xor_sync(gmask, sq, o);
+        if (sub == 0) norm2[c] = sq;
     }
+    bool done = false;    // my column already chosen
+    int mystep = N;       // ... at this step
+    double myscal = 0.0;  // ... and the scaling of its Householder vector
     __syncthreads();
-    for (int j = 0; j < N; ++j) {
-        // ---- pivot (every warp computes it: no barrier needed to publish it)
-        const int pc1 = lane + 32;
-        const double n0 = norm2[lane], n1 = HB ? norm2[pc1] : -1.0;
-        const int bi = warp_argmax2_64(n0, lane, n0 >= 0.0, n1, pc1, HB && n1 >= 0.0);
-        const double n2 = norm2[bi];  // exact |a(j:, bi)|^2 (recomputed after the previous reflector)
-        const bool piv_owner = owner && (bi >> 3) == warp;
-        const int qs = bi & 7;
-        if (piv_owner) {
-            // publish the RAW pivot column; the reflector scalars are derived from it by every warp on
-            // its own, overlapped with the dot products, instead of serially by this warp
-            double x = 0.0, y = 0.0;
+    for (int jb = 0; jb < TPC; ++jb) {
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                x = (q == qs) ? ca[q] : x;
-                y = (q == qs) ? cb[q] : y;
+        for (int k = 0; k < RPT; ++k) {
+            const int j = jb * RPT + k;  // row j = register k of the lanes with sub == jb
+            // ---- pivot (every warp computes it: no barrier needed to publish it)
+            const int pc1 = lane + 32;
+            const double n0 = norm2[lane], n1 = HB ? norm2[pc1] : -1.0;
+            const int bi = warp_argmax2_64(n0, lane, n0 >= 0.0, n1, pc1, HB && n1 >= 0.0);
+            const double n2 = norm2[bi];  // exact |a(j:, bi)|^2 (recomputed after the previous reflector)
+            const bool mine = (c == bi);
+            if (mine) {
+                // publish the RAW column (rows < j are exact zeros); everything else about the reflector is
+                // derived from it by the readers
+                double* xp = xraw + sub * XS;
+#pragma unroll
+                for (int k2 = 0; k2 < RPT; k2 += 2) *reinterpret_cast<double2*>(xp + k2) = make_double2(a[k2], a[k2 + 1]);
+                if (sub == 0) jpvt[j] = bi;
+                done = true;
+                mystep = j;
             }
-            xraw[rA] = x;
-            if (HB) xraw[rB] = y;
-            if (lane == 0) jpvt[j] = bi;
-        }
-        __syncthreads();
-        // retire the pivot column only now: every warp derives the pivot of this step from norm2 on its own, so
-        // the entry must not change before all of them have passed the barrier above (a warp held up for a few
-        // hundred cycles -- e.g. by a co-resident CTA in a tensor-core phase -- would otherwise see the column
-        // already retired and elect a different pivot)
-        if (piv_owner && lane == 0) norm2[bi] = -1.0;
-        if (piv_owner) done |= 1u << qs;
-        if (owner && (done != 0xffu || piv_owner)) {
-            const double xA = xraw[rA], xB = HB ? xraw[rB] : 0.0;
-            const double alpha = xraw[j];
-            // ---- dlarfg scalars (all lanes, redundantly; a latency chain that overlaps the reductions below):
-            // beta = -sign(alpha) |a(j:)|, tau = (beta - alpha) / beta, v = x / (alpha - beta) below the diagonal.
-            // |a(j:)|^2 is the exact partial norm the column was elected with; H = I if nothing is below.
-            const bool below = (rA > j && xA != 0.0) || (HB && rB > j && xB != 0.0);
-            const bool refl = __any_sync(DQ_FULL, below);
-            // With beta = -sign(alpha) nrm:  tau = 1 + |alpha| / nrm,  1 / (alpha - beta) = sign(alpha) / (|alpha| + nrm).
-            double hrs;
-            const double nrm = sqrt_newton(refl ? fmax(n2, alpha * alpha) : 1.0, &hrs);
-            const double beta = refl ? -copysign(nrm, alpha) : alpha;
-            const double t = refl ? fma(fabs(alpha), hrs + hrs, 1.0) : 0.0;
-            const double scal = refl ? copysign(rcp_newton(fabs(alpha) + nrm), alpha) : 0.0;
-            // ---- raw dot products x(j+1:)^T a_c and the row-j entries a(j, c)
-            const double mA = (rA > j) ? xA : 0.0, mB = (HB && rB > j) ? xB : 0.0;
-            double pr[8];
+            __syncthreads();
+            // retire the pivot column only now: every warp derives the pivot of this step from norm2 on its own, so
+            // the entry must not change before all of them have passed the barrier above (a warp held up for a few
+            // hundred cycles -- e.g. by a co-resident CTA in a tensor-core phase -- would otherwise see the column
+            // already retired and elect a different pivot)
+            if (mine && sub == 0) norm2[bi] = -1.0;
+            if (!done || mine) {
+                const double alpha = xraw[jb * XS + k];
+                // ---- dlarfg scalars (every thread; a latency chain that overlaps the dot products):
+                // beta = -sign(alpha) nrm, tau = (beta - alpha) / beta = 1 + |alpha| / nrm,
+                // v = x / (alpha - beta) = x sign(alpha) / (|alpha| + nrm) below the diagonal.
+                // A column that is already zero below the diagonal is still reflected (tau = 2, v = e_j: the sign
+                // of row j flips, LAPACK would take H = I) -- the same factorisation up to the sign freedom of
+                // Q / R rows; only an exactly zero column takes H = I.
+                const double nn = fmax(n2, alpha * alpha);
+                const bool refl = nn > 0.0;
+                double hrs;
+                const double nrm = sqrt_newton(refl ? nn : 1.0, &hrs);
+                const double beta = refl ? -copysign(nrm, alpha) : alpha;
+                const double tt = refl ? fma(fabs(alpha), hrs + hrs, 1.0) : 0.0;
+                const double scal = refl ? copysign(rcp_newton(fabs(alpha) + nrm), alpha) : 0.0;
+                if (!mine) {
+                    const double* xp = xraw + sub * XS;
+                    double x[RPT];
 #pragma unroll
-            for (int q = 0; q < 8; ++q) pr[q] = fma(mA, ca[q], mB * cb[q]);
-            if (lane == (j & 31)) {
+                    for (int k2 = 0; k2 < RPT; k2 += 2) {
+                        const double2 v = *reinterpret_cast<const double2*>(xp + k2);
+                        x[k2] = v.x;
+                        x[k2 + 1] = v.y;
+                    }
+                    if (sub == jb) x[k] = 0.0;  // row j itself enters through a(j, c) below
+                    double d0 = 0.0, d1 = 0.0, d2 = 0.0, d3 = 0.0;
 #pragma unroll
-                for (int q = 0; q < 8; ++q) ajbuf[cbase + q] = (j < 32) ? ca[q] : cb[q];
-            }
-            const double raw = warp_sum8_transposed(pr);
-            __syncwarp();
-            if ((lane & 3) == 0) wbuf[cbase + mycol] = t * fma(scal, raw, ajbuf[cbase + mycol]);  // tau (v^T a_c)
-            __syncwarp();
-            const double vA = (rA > j) ? xA * scal : ((rA == j) ? 1.0 : 0.0);
-            const double vB = (HB && rB > j) ? xB * scal : ((rB == j) ? 1.0 : 0.0);
-            double s[8];
+                    for (int k2 = 0; k2 < RPT; k2 += 4) {
+                        d0 = fma(x[k2], a[k2], d0);
+                        d1 = fma(x[k2 + 1], a[k2 + 1], d1);
+                        d2 = fma(x[k2 + 2], a[k2 + 2], d2);
+                        d3 = fma(x[k2 + 3], a[k2 + 3], d3);
+                    }
+                    double dot = (d0 + d1) + (d2 + d3);  // x(j+1:)^T a(j+1:, c), this lane's rows
 #pragma unroll
-            for (int q = 0; q < 8; ++q) {
-                const double w = ((done >> q) & 1u) ? 0.0 : wbuf[cbase + q];
-                ca[q] = fma(-w, vA, ca[q]);
-                cb[q] = fma(-w, vB, cb[q]);
-                const double ea = (rA > j) ? ca[q] : 0.0, eb = (HB && rB > j) ? cb[q] : 0.0;
-                s[q] = fma(ea, ea, eb * eb);
-            }
-            if (piv_owner) {
-                // the pivot column becomes (R(0..j-1, j), beta, v(j+1:))
-                const double x = (rA > j) ? vA : ((rA == j) ? beta : xA);
-                const double y = (rB > j) ? vB : ((rB == j) ? beta : xB);
+                    for (int o = 1; o < TPC; o <<= 1) dot += __shfl_xor_sync(gmask, dot, o);
+                    const double aj = __shfl_sync(gmask, a[k], grp | jb);  // a(j, c)
+                    const double w = tt * fma(scal, dot, aj);               // tau (v^T a_c)
+                    const double ws = w * scal;
 #pragma unroll
-                for (int q = 0; q < 8; ++q) {
-                    ca[q] = (q == qs) ? x : ca[q];
-                    cb[q] = (q == qs) ? y : cb[q];
+                    for (int k2 = 0; k2 < RPT; ++k2) a[k2] = fma(-ws, x[k2], a[k2]);
+                    if (sub == jb) {
+                        A[j + (size_t)c * LDT] = a[k] - w;  // R(j, c) is final: retire the row
+                        a[k] = 0.0;
+                    }
+                    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+#pragma unroll
+                    for (int k2 = 0; k2 < RPT; k2 += 4) {
+                        s0 = fma(a[k2], a[k2], s0);
+                        s1 = fma(a[k2 + 1], a[k2 + 1], s1);
+                        s2 = fma(a[k2 + 2], a[k2 + 2], s2);
+                        s3 = fma(a[k2 + 3], a[k2 + 3], s3);
+                    }
+                    double sq = (s0 + s1) + (s2 + s3);  // exact |a(j+1:, c)|^2
+#pragma unroll
+                    for (int o = 1; o < TPC; o <<= 1) sq += __shfl_xor_sync(gmask, sq, o);
+                    if (sub == 0) norm2[c] = sq;
+                } else {
+                    // my column is the pivot column: it becomes (R(0..j-1, j) [already in the tile], beta, v(j+1:));
+                    // the scaling of v = x / (alpha - beta) is applied when the column is stored at the end
+                    myscal = scal;
+                    if (sub == jb) {
+                        A[j + (size_t)c * LDT] = beta;
+                        a[k] = 0.0;
+                    }
+                    if (sub == 0) tau[j] = tt;
                 }
-                if (lane == 0) tau[j] = t;
             }
-            const double nn = warp_sum8_transposed(s);  // exact |a(j+1:, c)|^2
-            if ((lane & 3) == 0 && !((done >> mycol) & 1u)) norm2[cbase + mycol] = nn;
+            __syncthreads();
         }
-        __syncthreads();
     }
-    if (owner) {
+    // rows below the diagonal entry of each column come from the registers (the rows above were retired into the tile)
+    {
+        double* cp = A + (size_t)c * LDT + sub * RPT;
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            double* cp = A + (size_t)(cbase + q) * LDT;
-            cp[rA] = ca[q];
-            if (HB) cp[rB] = cb[q];
-        }
+        for (int k = 0; k < RPT; ++k)
+            if (sub * RPT + k > mystep) cp[k] = a[k] * myscal;
     }
     __syncthreads();
 }

@@ -400,7 +400,14 @@ __device__ void form_q_tile(double* __restrict__ Q, const double* __restrict__ V
     const int rA = lane, rB = lane + 32;
     const bool hasA = rA < N, hasB = rB < N;
     // four columns per warp pass: c, c+1, c+2, c+3 share every reflector load
-    for (int cb = 4 * warp; cb < N; cb += 4 * nwarps) {
+    // A column's cost grows with its index (column c takes reflectors c .. 0): the passes pair the short
+    // column groups of a warp with long ones (4 w, then N - 4 - 4 w, ...), so that every warp applies
+    // about the same number of reflectors and the closing barrier waits for nobody in particular.
+    const int ngroups = N / 4;
+    for (int gi = warp; gi < ngroups; gi += nwarps) {
+        const int pass = gi / nwarps;
+        const int cb = 4 * ((pass & 1) ? (pass + 1) * nwarps - 1 - warp : gi);
+        if (cb >= N || cb < 0) continue;
         double qa[4], qb[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
@@ -488,6 +495,7 @@ __device__ void lu_tile(double* __restrict__ A, int* __restrict__ perm, double* 
         double* Lp = A + (size_t)(pb & 1) * 8 * N;  // [jj][row] multipliers of step 8 pb + jj
         int* pv = pvbuf + (pb & 1) * 8;             // pivot row of step 8 pb + jj
         if (warp == pb) {
+            int bad = 0;
 #pragma unroll
             for (int jj = 0; jj < 8; ++jj) {
                 const int j = 8 * pb + jj;
@@ -515,14 +523,17 @@ __device__ void lu_tile(double* __restrict__ A, int* __restrict__ perm, double* 
                     pv[jj] = p;
                     perm[j] = p;
                     rdiag[j] = rinv;
-                    if (piv == 0.0 && *info == 0) *info = j + 1;
                 }
+                bad = (piv == 0.0 && bad == 0) ? j + 1 : bad;  // first exactly singular pivot of this panel
 #pragma unroll
                 for (int q = jj + 1; q < 8; ++q) {
                     const double u = __shfl_sync(DQ_FULL, (p < 32) ? ca[q] : cb[q], p & 31);
                     ca[q] = fma(-lA, u, ca[q]);
                     cb[q] = fma(-lB, u, cb[q]);
                 }
+            }
+            if (bad != 0) {  // warp-uniform, rare; panels run one after the other, so the first one to report wins
+                if (lane == 0 && *info == 0) *info = bad;
             }
         }
         __syncthreads();

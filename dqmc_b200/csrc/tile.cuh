@@ -597,7 +597,7 @@ __device__ void lu_tile(double* __restrict__ A, int* __restrict__ perm, double* 
 // reciprocal pivots, which does not depend on the data).  Uses perm / rdiag from lu_tile.  All threads
 // of the CTA may call; the caller synchronises before and after.
 template <int N>
-__device__ __noinline__ void lu_solve_tile(const double* __restrict__ A, const int* __restrict__ perm, const double* __restrict__ rdiag,
+__device__ __forceinline__ void lu_solve_tile(const double* __restrict__ A, const int* __restrict__ perm, const double* __restrict__ rdiag,
                                            double* __restrict__ Bm, int rsB, int csB) {
     static_assert(N == 32 || N == 64, "lu_solve_tile layout");
     constexpr int LDT = Tile<N>::LDT;

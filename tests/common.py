@@ -12,6 +12,11 @@ CONFIGS = {
     "R7": (7, 5, 3.0, 1.0, 0.2, 3.0, 23, 6),       # odd N, ragged last block (nt % n_stab != 0)
     "F32": (8, 4, 5.0, 1.0, 0.1, 2.3, 23, 5),      # N = 32 fast path, ragged last block
     "C3s": (16, 16, 6.0, 1.0, 0.0, 1.0, 10, 5),    # 16x16 (N = 256): L2-resident tiles, DMMA generic GEMM
+    # atomic limit t = 0 on the fast path: exp(-dtau K) = I, every B and G diagonal -- the pivoted QR meets columns that
+    # are already zero below the diagonal (reflected with tau = 2 by the fast path, H = I in LAPACK), LU pivots sit on
+    # the diagonal, and every triangular solve is trivial
+    "T0": (8, 8, 4.0, 0.0, 0.0, 2.0, 20, 5),
+    "T0_32": (8, 4, 3.0, 0.0, 0.0, 1.5, 15, 4),
 }
 
 

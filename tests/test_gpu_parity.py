@@ -26,7 +26,7 @@ def _setup(name, seeds, delay_k=0):
     return cfg, pairs, ctx
 
 
-@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "C2s", "F32"])
+@pytest.mark.parametrize("name", ["C0", "C1s", "R7", "C2s", "F32", "T0", "T0_32"])
 def test_init_stacks_and_green(name):
     cfg, pairs, ctx = _setup(name, [11, 12, 13])
     ctx.init_stacks()
@@ -103,7 +103,7 @@ def test_local_update_teacher_forced(name, delay_k):
 
 
 @pytest.mark.parametrize("name,n_sweeps,delay_k", [("C0", 3, 0), ("C1s", 3, 0), ("R7", 3, 0), ("C2s", 1, 0), ("F32", 3, 0), ("C1", 1, 0),
-                                                   ("C3s", 1, 0), ("R7", 2, 4), ("C2s", 1, 8), ("C0", 2, 16), ("C3s", 1, 32)])
+                                                   ("C3s", 1, 0), ("R7", 2, 4), ("C2s", 1, 8), ("C0", 2, 16), ("C3s", 1, 32), ("T0", 2, 0), ("T0_32", 2, 0)])
 def test_trajectory(name, n_sweeps, delay_k):
     """Free-running sweeps on the same RNG tape: identical accept decisions / fields; G compared at
     the end of each half sweep (a stabilisation point, where G is a function of the fields only).

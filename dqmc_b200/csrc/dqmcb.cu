@@ -561,6 +561,34 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
     p.invexpK = ctx->d_invexpK;
     p.expK_half = ctx->d_expKh;
     p.invexpK_half = ctx->d_invexpKh;
+    p.kron = nullptr;
+    {
+        // Kronecker structure of exp(-dtau K) for the 8 x 8 lattice (site i = x + 8 y): E = Ey (x) Ex with
+        // Ex = E[(0,x),(0,x')] and Ey = E[(y,0),(y',0)] / E[0,0]; accepted only if it reproduces E to 1e-14 of its
+        // largest entry (any other geometry, anisotropy that breaks the product form, or a user matrix: dense path)
+        const char* nk = getenv("DQMCB_NO_KRON");
+        if (N == 64 && !(nk && nk[0] == (char)49) && expK[0] != 0.0) {
+            double f[128];
+            for (int b = 0; b < 8; ++b)
+                for (int a = 0; a < 8; ++a) {
+                    f[a + 8 * b] = expK[(size_t)a + (size_t)b * N];                                  // Ex(a, b)
+                    f[64 + a + 8 * b] = expK[(size_t)(8 * a) + (size_t)(8 * b) * N] / expK[0];       // Ey(a, b)
+                }
+            double emax = 0.0, dmax = 0.0;
+            for (int c = 0; c < N; ++c)
+                for (int r = 0; r < N; ++r) {
+                    const double e = expK[(size_t)r + (size_t)c * N];
+                    const double k = f[64 + (r >> 3) + 8 * (c >> 3)] * f[(r & 7) + 8 * (c & 7)];
+                    emax = std::max(emax, std::fabs(e));
+                    dmax = std::max(dmax, std::fabs(e - k));
+                }
+            if (dmax <= 1e-14 * emax) {
+                CKC(cudaMalloc(&ctx->d_kron, sizeof(f)));
+                CKC(cudaMemcpy(ctx->d_kron, f, sizeof(f), cudaMemcpyHostToDevice));
+                p.kron = ctx->d_kron;
+            }
+        }
+    }
     CKC(cudaMalloc(&p.fields, (size_t)W * nt * N));
     CKC(cudaMemset(p.fields, 0, (size_t)W * nt * N));
     CKC(cudaMalloc(&p.G, W * nn * 8));
@@ -644,6 +672,7 @@ void dqmcb_destroy(dqmcb_ctx* ctx) {
     cudaFree(ctx->d_invexpK);
     cudaFree(ctx->d_expKh);
     cudaFree(ctx->d_invexpKh);
+    cudaFree(ctx->d_kron);
     cudaFree(p.fields);
     cudaFree(p.G);
     cudaFree(p.Bbar);

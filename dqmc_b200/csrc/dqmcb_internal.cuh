@@ -25,6 +25,9 @@ struct Params {
     const double* invexpK;
     const double* expK_half;
     const double* invexpK_half;
+    // exp(-dtau K) = Ey (x) Ex on a square lattice with site index x + L1 y (K = Kx (+) Ky): 8 x 8 factors, column-major,
+    // [0..63] = Ex, [64..127] = Ey; null unless N = 64 and the host verified the structure to 1e-14 (fast-path Bbar chain)
+    const double* kron;
     int8_t* fields;   // [W][nt][N]
     double* G;        // [W][N*N]   current equal-time Green's function, column-major, ld = N
     double* Bbar;     // [W][N*N]
@@ -73,7 +76,7 @@ struct dqmcb_ctx {
     std::string err;
     bool stacks_ready = false, green_ready = false;
     // owned device allocations
-    double *d_expK = nullptr, *d_invexpK = nullptr, *d_expKh = nullptr, *d_invexpKh = nullptr;
+    double *d_expK = nullptr, *d_invexpK = nullptr, *d_expKh = nullptr, *d_invexpKh = nullptr, *d_kron = nullptr;
     uint8_t *d_tape_perm = nullptr, *d_tape_k = nullptr;
     double* d_tape_u = nullptr;
     size_t tape_cap = 0;  // visits allocated

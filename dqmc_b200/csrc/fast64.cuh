@@ -203,9 +203,15 @@ __device__ void f_bbar(const Params& p, FWork<N>& wk, int walker, int i_stack) {
     const int l1 = min(l0 + p.n_stab, p.nt);
     const int8_t* f = p.fields + ((size_t)walker * p.nt) * N;
     const int m = l1 - l0;
-    double* cur = (m & 1) ? wk.t[0] : wk.t[1];
-    double* oth = (m & 1) ? wk.t[1] : wk.t[0];
+    // Kronecker chain (8 x 8 lattice): in place in t[0], exp(g eta) of the whole block staged in the idle tile t[1]
+    const bool kron = (N == 64) && p.kron != nullptr && (m * N <= Tile<N>::ELEMS);
+    double* cur = (kron || (m & 1)) ? wk.t[0] : wk.t[1];
+    double* oth = (kron || (m & 1)) ? wk.t[1] : wk.t[0];
     __syncthreads();
+    // in-place chain: exp(g eta) of every slice of the block is staged up front in the idle tile t[1] (one exposure of
+    // the HBM latency of the field bytes instead of one per slice)
+    if (kron)
+        for (int e = threadIdx.x; e < m * N; e += blockDim.x) wk.t[1][e] = p.lut_ev[f[(size_t)l0 * N + e]];
     tile_fetch<N>(wk, wk.t[2], p.expK);
     for (int i = threadIdx.x; i < N; i += blockDim.x) wk.sv[0][i] = p.lut_ev[f[(size_t)l0 * N + i]];
     __syncthreads();
@@ -214,6 +220,72 @@ __device__ void f_bbar(const Params& p, FWork<N>& wk, int walker, int i_stack) {
         cur[r + (size_t)c * LDT] = wk.sv[0][r] * wk.t[2][r + (size_t)c * LDT];
     }
     __syncthreads();
+    if (kron) {
+        // exp(-dtau K) = Ey (x) Ex: B_l X = diag(ev_l) (Ey (x) I)(I (x) Ex) X as two in-place passes of 8 x 8 tensor-core
+        // products with the factor held in registers (256 DMMA.8x8x4 per slice instead of 1024):
+        //   pass 1: every 8 x 8 block (rows 8y.., columns 8cb..) <- Ex * block;
+        //   pass 2: every column c, viewed as the 8 x 8 matrix W(x, y') = X[x + 8 y', c], <- W Ey^T, scaled by ev.
+        // A task's inputs are fully loaded (warp-collective DMMA) before its outputs are stored: in place is safe.
+        // Both passes act on each COLUMN separately (V <- Ex V Ey^T for the 8 x 8 matrix V(x, y) = X[x + 8 y, c]), so warp q
+        // owns the columns [8q, 8q+8) for the whole chain: no block barrier between passes or slices, only __syncwarp.
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, gr = lane >> 2, tg = lane & 3;
+        const double ex0 = p.kron[gr + 8 * tg], ex1 = p.kron[gr + 8 * (tg + 4)];            // A fragment: Ex(gr, k)
+        const double ey0 = p.kron[64 + gr + 8 * tg], ey1 = p.kron[64 + gr + 8 * (tg + 4)];  // B fragment: Ey^T(k, gr) = Ey(gr, k)
+        double* X = cur;
+        for (int l = l0 + 1; l < l1; ++l) {
+            const double* evl = wk.t[1] + (size_t)(l - l0) * N;
+            // all loads of a pass are issued before its first DMMA (8 independent tasks per warp)
+            constexpr int NW = kThreads / 32, NT = 64 / NW;
+            double b0[NT], b1[NT], c0[NT], c1[NT];
+#pragma unroll
+            for (int u = 0; u < NT; ++u) {
+                const int y = u, cb = warp;  // this warp's 8 columns, every row block
+                const double* bp = X + (8 * y + tg) + (size_t)(8 * cb + gr) * LDT;
+                b0[u] = bp[0];
+                b1[u] = bp[4];
+            }
+#pragma unroll
+            for (int u = 0; u < NT; ++u) {
+                c0[u] = c1[u] = 0.0;
+                dmma884(c0[u], c1[u], ex0, b0[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < NT; ++u) dmma884(c0[u], c1[u], ex1, b1[u]);
+#pragma unroll
+            for (int u = 0; u < NT; ++u) {
+                const int y = u, cb = warp;
+                double* cp = X + (8 * y + gr) + (size_t)(8 * cb + 2 * tg) * LDT;
+                cp[0] = c0[u];
+                cp[LDT] = c1[u];
+            }
+            __syncwarp();
+#pragma unroll
+            for (int u = 0; u < NT; ++u) {
+                const double* colp = X + (size_t)(NT * warp + u) * LDT;
+                b0[u] = colp[gr + 8 * tg];
+                b1[u] = colp[gr + 8 * (tg + 4)];
+            }
+#pragma unroll
+            for (int u = 0; u < NT; ++u) {
+                c0[u] = c1[u] = 0.0;
+                dmma884(c0[u], c1[u], b0[u], ey0);
+            }
+#pragma unroll
+            for (int u = 0; u < NT; ++u) dmma884(c0[u], c1[u], b1[u], ey1);
+            {
+                const int r0 = gr + 16 * tg;  // row x + 8 y of the output element (x = gr, y = 2 tg + j)
+                const double e0 = evl[r0], e1 = evl[r0 + 8];
+#pragma unroll
+                for (int u = 0; u < NT; ++u) {
+                    double* colp = X + (size_t)(NT * warp + u) * LDT;
+                    colp[r0] = e0 * c0[u];
+                    colp[r0 + 8] = e1 * c1[u];
+                }
+            }
+            __syncwarp();
+        }
+        return;
+    }
     for (int l = l0 + 1; l < l1; ++l) {
         for (int i = threadIdx.x; i < N; i += blockDim.x) wk.sv[0][i] = p.lut_ev[f[(size_t)l * N + i]];
         __syncthreads();

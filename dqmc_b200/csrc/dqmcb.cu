@@ -567,22 +567,29 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
         // Ex = E[(0,x),(0,x')] and Ey = E[(y,0),(y',0)] / E[0,0]; accepted only if it reproduces E to 1e-14 of its
         // largest entry (any other geometry, anisotropy that breaks the product form, or a user matrix: dense path)
         const char* nk = getenv("DQMCB_NO_KRON");
-        if (N == 64 && !(nk && nk[0] == (char)49) && expK[0] != 0.0) {
-            double f[128];
-            for (int b = 0; b < 8; ++b)
-                for (int a = 0; a < 8; ++a) {
-                    f[a + 8 * b] = expK[(size_t)a + (size_t)b * N];                                  // Ex(a, b)
-                    f[64 + a + 8 * b] = expK[(size_t)(8 * a) + (size_t)(8 * b) * N] / expK[0];       // Ey(a, b)
-                }
-            double emax = 0.0, dmax = 0.0;
-            for (int c = 0; c < N; ++c)
-                for (int r = 0; r < N; ++r) {
-                    const double e = expK[(size_t)r + (size_t)c * N];
-                    const double k = f[64 + (r >> 3) + 8 * (c >> 3)] * f[(r & 7) + 8 * (c & 7)];
-                    emax = std::max(emax, std::fabs(e));
-                    dmax = std::max(dmax, std::fabs(e - k));
-                }
-            if (dmax <= 1e-14 * emax) {
+        if (N == 64 && !(nk && nk[0] == (char)49) && expK[0] != 0.0 && invexpK[0] != 0.0) {
+            double f[256];  // Ex, Ey (of expK), Exi, Eyi (of invexpK), 8 x 8 column-major each
+            bool ok = true;
+            for (int which = 0; which < 2 && ok; ++which) {
+                const double* E = which ? invexpK : expK;
+                double* fx = f + 128 * which;
+                double* fy = fx + 64;
+                for (int b = 0; b < 8; ++b)
+                    for (int a = 0; a < 8; ++a) {
+                        fx[a + 8 * b] = E[(size_t)a + (size_t)b * N];                         // Fx(a, b)
+                        fy[a + 8 * b] = E[(size_t)(8 * a) + (size_t)(8 * b) * N] / E[0];      // Fy(a, b)
+                    }
+                double emax = 0.0, dmax = 0.0;
+                for (int c = 0; c < N; ++c)
+                    for (int r = 0; r < N; ++r) {
+                        const double e = E[(size_t)r + (size_t)c * N];
+                        const double k = fy[(r >> 3) + 8 * (c >> 3)] * fx[(r & 7) + 8 * (c & 7)];
+                        emax = std::max(emax, std::fabs(e));
+                        dmax = std::max(dmax, std::fabs(e - k));
+                    }
+                ok = dmax <= 1e-14 * emax;
+            }
+            if (ok) {
                 CKC(cudaMalloc(&ctx->d_kron, sizeof(f)));
                 CKC(cudaMemcpy(ctx->d_kron, f, sizeof(f), cudaMemcpyHostToDevice));
                 p.kron = ctx->d_kron;

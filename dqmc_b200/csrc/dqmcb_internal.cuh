@@ -26,7 +26,8 @@ struct Params {
     const double* expK_half;
     const double* invexpK_half;
     // exp(-dtau K) = Ey (x) Ex on a square lattice with site index x + L1 y (K = Kx (+) Ky): 8 x 8 factors, column-major,
-    // [0..63] = Ex, [64..127] = Ey; null unless N = 64 and the host verified the structure to 1e-14 (fast-path Bbar chain)
+    // [0..63] = Ex, [64..127] = Ey, [128..255] the same for exp(+dtau K); null unless N = 64 and the host verified the
+    // structure of both to 1e-14 (fast-path Bbar chain and wraps)
     const double* kron;
     int8_t* fields;   // [W][nt][N]
     double* G;        // [W][N*N]   current equal-time Green's function, column-major, ld = N

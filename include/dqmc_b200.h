@@ -56,7 +56,10 @@ typedef struct {
 
 /* ---- lifetime ------------------------------------------------------------------------------- */
 /* AttractiveHubbard ctor + DQMC ctor (source/model.cpp:3-36, source/dqmc.cpp:5-36).  expK / invexpK
- * are host N x N column-major exp(-/+ dtau K); K itself is built on the host (source/model.cpp:39-60). */
+ * are host N x N column-major exp(-/+ dtau K); K itself is built on the host (source/model.cpp:39-60).
+ * For N = 64 the matrices are tested for the product form Ey (x) Ex of the 8 x 8 square lattice (site x + 8 y,
+ * include/lattice.h:100-107); if both reproduce to 1e-14 the fast path applies them as 8 x 8 factors (a quarter of the
+ * flops of the dense product, results equal to rounding order), otherwise -- or with env DQMCB_NO_KRON=1 -- densely. */
 int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* invexpK, dqmcb_ctx** out);
 void dqmcb_destroy(dqmcb_ctx* ctx);
 const char* dqmcb_last_error(const dqmcb_ctx* ctx); /* ctx may be NULL: last create() error */

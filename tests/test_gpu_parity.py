@@ -280,6 +280,48 @@ def test_walker_groups_on_streams_are_equivalent(monkeypatch):
     assert np.array_equal(out[0][2], out[1][2])
 
 
+def test_kronecker_factor_path_equals_dense_path(monkeypatch):
+    """On the 8x8 lattice exp(-+dtau K) = Ey (x) Ex and the fast path applies the 8x8 factors (Bbar chain, wraps);
+    DQMCB_NO_KRON=1 forces the dense products.  Same Philox keys: teacher-forced pieces (block product, one wrap)
+    agree to 1e-12 / 1e-10, and a free-running sweep takes identical decisions with G equal at the stabilisation point.
+    A matrix that is NOT of product form (one entry perturbed by 1e-9) must fall back to the dense path by itself."""
+    from dqmc_b200 import capi
+
+    cfg = CONFIGS["C1s"]
+    W = 8
+    m, _ = make_oracle(cfg, 5)
+    rng = np.random.default_rng(19)
+    f0 = rng.integers(0, 4, size=(W, cfg[6], cfg[0] * cfg[1]), dtype=np.int8)
+    bad = m.expK.copy()
+    bad[3, 17] *= 1.0 + 1e-9
+    out = []
+    for env, expK in ((None, m.expK), ("1", m.expK), (None, bad)):
+        if env is None:
+            monkeypatch.delenv("DQMCB_NO_KRON", raising=False)
+        else:
+            monkeypatch.setenv("DQMCB_NO_KRON", env)
+        ctx = make_ctx(cfg, W, expK, m.invexpK)
+        ctx.set_fields(f0)
+        ctx.rng_mode(capi.RNG_PHILOX, 77)
+        ctx.init_stacks()
+        ctx.init_greenfunctions()
+        B = ctx.block_product(1)
+        ctx.wrap_forward(0)
+        Gw = ctx.get_G()
+        ctx.init_greenfunctions()
+        ctx.sweep_0_to_beta()
+        ctx.sweep_beta_to_0()
+        out.append((B, Gw, ctx.get_fields(), ctx.get_G(), ctx.get_stats()[0]))
+        ctx.close()
+    kron, dense, fallback = out
+    assert rel_err(kron[0], dense[0]) < 1e-12 and rel_err(kron[1], dense[1]) < TOL  # G carries the stack's conditioning
+    assert not np.array_equal(kron[0], dense[0])  # the factor path really ran (different rounding order)
+    assert np.array_equal(kron[2], dense[2]) and np.array_equal(kron[4], dense[4])
+    assert rel_err(kron[3], dense[3]) < 1e-9
+    # perturbed matrix: dense path on its own; compare with the forced-dense run of the exact matrix only loosely
+    assert rel_err(fallback[0], dense[0]) < 1e-7
+
+
 def test_delayed_updates_with_tiles_in_global_memory_and_shared_sms():
     """Delayed rank-k updates at a size where G no longer fits beside the factors in shared memory
     (N=144, k=32: G lives in the global workspace) and with more walkers than SMs (two CTAs per SM):

@@ -289,7 +289,7 @@ def program_case():
     np.savez_compressed(os.path.join(HERE, "program.npz"), **out)
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and not (len(sys.argv) > 1 and sys.argv[1] == "full"):
     assert ref.build(), "oracle/_ref could not be built (needs /root/reference)"
     for nm, cfg in CASES.items():
         trajectory_case(nm, cfg)
@@ -300,3 +300,68 @@ if __name__ == "__main__":
     unequal_case()
     program_case()
     print("golden fixtures written to", HERE)
+
+
+# ---------------------------------------------------------------------------------------------------
+# Full-size BASELINE configurations: free-running trajectories of the reference at the
+# stated beta / nt.  The RNG stream is NOT stored: it is std::mt19937(seed), which the device regenerates
+# (DQMCB_RNG_MT19937) and oracle/dqmc_oracle.py restates.  Written to traj_full_<name>.npz by
+#     python tests/golden/make_golden.py full
+# ---------------------------------------------------------------------------------------------------
+FULL_CASES = {
+    # name: (L1, L2, U, t, mu, beta, nt, n_stab, seed, n_sweeps, keep_G = number of trailing half sweeps whose G is stored)
+    "c1": (8, 8, 4.0, 1.0, 0.0, 8.0, 80, 10, 8101, 10, 20),
+    "c2": (12, 12, 4.0, 1.0, 0.0, 10.0, 100, 10, 12101, 2, 4),
+    "c2n5": (12, 12, 4.0, 1.0, 0.0, 10.0, 100, 5, 12105, 2, 2),
+    "c3n5": (16, 16, 6.0, 1.0, 0.0, 16.0, 160, 5, 16105, 2, 2),
+    # n_stab = 10 at U = 6, beta = 16: the reference's own check_error reaches O(1) within one sweep, so a
+    # trajectory is meaningless there; only the start-up state (a pure function of the fields) is pinned
+    "c3": (16, 16, 6.0, 1.0, 0.0, 16.0, 160, 10, 16110, 0, 1),
+}
+
+
+def full_case(name, cfg):
+    L1, L2, U, t, mu, beta, nt, n_stab, seed, n_sweeps, keep = cfg
+    s = ref.RefSim(L1, L2, U, t, mu, beta, nt, n_stab, seed)
+    out = {
+        "cfg": np.array([L1, L2, U, t, mu, beta, nt, n_stab, seed, n_sweeps], dtype=np.float64),
+        "fields0": s.fields().astype(np.int8),
+        "expK": s.expK(), "invexpK": s.invexpK(),
+        "G0_diag": np.diag(s.G(0)).copy(), "logdet0": np.array(s.logdet()),
+        "stack0_d": np.stack([np.sort(s.stack(i)[1]) for i in range(s.n_stack)]),
+    }
+    if keep >= 2 * n_sweeps:
+        out["G0"] = s.G(0)
+    if n_sweeps == 0:
+        np.savez_compressed(os.path.join(HERE, f"traj_full_{name}.npz"), **out)
+        print(name, "init only, bytes", os.path.getsize(os.path.join(HERE, f"traj_full_{name}.npz")))
+        return
+    fs, lds, Gs, Gd, errs = [], [], [], [], []
+    tok = silence_stderr()
+    try:
+        for _ in range(n_sweeps):
+            for half in range(2):
+                (s.sweep_fwd if half == 0 else s.sweep_bwd)()
+                G = s.G(nt if half == 0 else 0)
+                fs.append(s.fields().astype(np.int8)); lds.append(s.logdet()); Gs.append(G); Gd.append(np.diag(G).copy())
+                errs.append((s.max_err(), s.mean_err()))
+    finally:
+        restore_stderr(tok)
+    out["traj_fields"] = np.stack(fs); out["traj_logdet"] = np.array(lds); out["traj_G_diag"] = np.stack(Gd)
+    out["traj_G_tail"] = np.stack(Gs[-keep:])  # G at the end of the last `keep` half sweeps
+    out["traj_err"] = np.array(errs)             # (running max, running mean) of check_error after each half sweep
+    out["traj_acc_rate"] = np.array(s.acc_rate())
+    out["stack_d"] = np.stack([np.sort(s.stack(i)[1]) for i in range(s.n_stack)])
+    out["traj_action"] = np.array(s.global_action())
+    o = s.observables()
+    out["traj_obs"] = np.array(o[:3])
+    np.savez_compressed(os.path.join(HERE, f"traj_full_{name}.npz"), **out)
+    print(name, "acc", float(out["traj_acc_rate"]), "check_error max/mean", errs[-1], "bytes",
+          os.path.getsize(os.path.join(HERE, f"traj_full_{name}.npz")))
+
+
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "full":
+    for nm, cfg in FULL_CASES.items():
+        if len(sys.argv) > 2 and nm not in sys.argv[2:]:
+            continue
+        full_case(nm, cfg)

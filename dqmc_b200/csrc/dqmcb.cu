@@ -588,6 +588,16 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
                         dmax = std::max(dmax, std::fabs(e - k));
                     }
                 ok = dmax <= 1e-14 * emax;
+                // the row-wise passes of the wraps (kron_right16) and the transposed chain of the backward stabilisation feed
+                // F(gr, tg) where F(tg, gr) is meant: they need SYMMETRIC factors.  A matrix of product form that is not
+                // symmetric (a caller-supplied exp(-dtau K)) takes the dense path.
+                double smax = 0.0;
+                for (int b = 0; b < 8; ++b)
+                    for (int a = 0; a < 8; ++a) {
+                        smax = std::max(smax, std::fabs(fx[a + 8 * b] - fx[b + 8 * a]));
+                        smax = std::max(smax, std::fabs(fy[a + 8 * b] - fy[b + 8 * a]));
+                    }
+                ok = ok && smax <= 1e-14 * std::max(1.0, emax / std::fabs(E[0])) * std::fabs(fx[0]);
             }
             if (ok) {
                 CKC(cudaMalloc(&ctx->d_kron, sizeof(f)));
@@ -652,6 +662,11 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
         }
     }
     CKC(fast64_setup(ctx));
+    {
+        const char* s2e = getenv("DQMCB_STAB2");  // "0": keep the first-generation stabilisation kernel (A/B comparisons)
+        ctx->use_stab2 = N == 64 && p.kron != nullptr && cfg->n_stab <= dq::s2::MAX_SLICES && !ctx->force_generic &&
+                         !(s2e && s2e[0] == (char)48);
+    }
     {
         const char* gs = getenv("DQMCB_STREAMS");
         int ng = gs ? atoi(gs) : 2;

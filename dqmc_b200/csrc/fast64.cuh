@@ -467,6 +467,7 @@ __global__ void __launch_bounds__(kThreads, 2) kf_init_green(Params p) {
 
 }  // namespace dq
 
+#include "stab2.cuh"
 #include "prop64.cuh"
 
 // =====================================================================================================
@@ -494,6 +495,7 @@ static cudaError_t fast_setup_n() {
     if ((e = cudaFuncSetAttribute(dq::kf_stabilize<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(dq::kf_init_stacks<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(dq::kf_init_green<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, sm)) != cudaSuccess) return e;
+    if (N == 64 && (e = dq::s2::setup()) != cudaSuccess) return e;
     return dq::fast_prop_setup<N>();
 }
 
@@ -513,6 +515,13 @@ static inline void fast_stabilize(dqmcb_ctx* ctx, int l, int dir, int w0 = 0, in
     p.w0 = w0;
     p.w1 = (w1 < 0) ? p.W : w1;
     if (!st) st = ctx->stream;
+    if (ctx->use_stab2) {  // warp pair per walker, four walkers per SM (stab2.cuh)
+        if (dir > 0)
+            dq::s2::kf2_stabilize<1><<<p.w1 - p.w0, dq::s2::NTH, dq::s2::Smem::TOTAL, st>>>(p, l);
+        else
+            dq::s2::kf2_stabilize<-1><<<p.w1 - p.w0, dq::s2::NTH, dq::s2::Smem::TOTAL, st>>>(p, l);
+        return;
+    }
     FAST_DISPATCH(p.N, (dq::kf_stabilize<FN><<<p.w1 - p.w0, dq::kThreads, dq::StabSmem<FN>::TOTAL, st>>>(p, l, dir)));
 }
 static inline void fast_init_stacks(dqmcb_ctx* ctx) {

@@ -27,6 +27,9 @@ using namespace dq;
 // Propagate + Metropolis over `n_slices` consecutive slices starting at l_first, in sweep direction
 // dir (+1: wrap then flip, source/dqmc.cpp:357-366; -1: flip then wrap, source/dqmc.cpp:416-426).
 // flags: bit0 = do wraps, bit1 = do flips.
+// BIG: instantiation for N >= 128 (large-tile tensor-core products, one CTA per SM); the other one keeps its register count
+// for the small lattices, where two CTAs share an SM.
+template <bool BIG>
 __global__ void __launch_bounds__(kThreads) k_propagate(Params p, int l_first, int n_slices, int dir, unsigned long long visit0, int flags) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int w = blockIdx.x, n = p.N;
@@ -66,12 +69,12 @@ __global__ void __launch_bounds__(kThreads) k_propagate(Params p, int l_first, i
                 s_iev[i] = p.lut_iev[s_f[i]];
             }
             __syncthreads();
-            dev_wrap_forward(p, n, g, ld, t, ld, s_ev, s_iev);
+            dev_wrap_forward<BIG>(p, n, g, ld, t, ld, s_ev, s_iev);
         }
         if (flags & 2) {
             load_visit_draws(p, w, visit0 + s, s_perm, s_k, s_u, s_key);
             if (p.delay_k > 1)
-                accepted += dev_local_update_delayed(p, n, g, ld, s_f, s_perm, s_k, s_u, s_diag, dU, dV, p.delay_k);
+                accepted += dev_local_update_delayed<BIG>(p, n, g, ld, s_f, s_perm, s_k, s_u, s_diag, dU, dV, p.delay_k);
             else
                 accepted += dev_local_update(p, n, g, ld, s_f, s_perm, s_k, s_u, s_ucol, s_vrow);
             __syncthreads();
@@ -83,7 +86,7 @@ __global__ void __launch_bounds__(kThreads) k_propagate(Params p, int l_first, i
                 s_iev[i] = p.lut_iev[s_f[i]];
             }
             __syncthreads();
-            dev_wrap_backward(p, n, g, ld, t, ld, s_ev, s_iev);
+            dev_wrap_backward<BIG>(p, n, g, ld, t, ld, s_ev, s_iev);
         }
     }
     __syncthreads();
@@ -645,7 +648,8 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
         dqmcb_destroy(ctx);
         return DQMCB_EINVAL;
     }
-    CKC(cudaFuncSetAttribute(k_propagate, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_prop));
+    CKC(cudaFuncSetAttribute(k_propagate<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_prop));
+    CKC(cudaFuncSetAttribute(k_propagate<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_prop));
     CKC(cudaFuncSetAttribute(k_bbar, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
     CKC(cudaFuncSetAttribute(k_stabilize, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
     CKC(cudaFuncSetAttribute(k_init_stacks, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
@@ -1019,7 +1023,10 @@ static int launch_propagate(dqmcb_ctx* ctx, int l_first, int n_slices, int dir, 
     TimeScope ts(ctx, DQMCB_K_PROPAGATE);
     ctx->n_launches += 1;
     if (fast64_available(ctx)) return fast64_propagate(ctx, p, l_first, n_slices, dir, v0, flags);
-    k_propagate<<<p.W, kThreads, ctx->smem_prop, ctx->stream>>>(p, l_first, n_slices, dir, v0, flags);
+    if (p.N >= 128)
+        k_propagate<true><<<p.W, kThreads, ctx->smem_prop, ctx->stream>>>(p, l_first, n_slices, dir, v0, flags);
+    else
+        k_propagate<false><<<p.W, kThreads, ctx->smem_prop, ctx->stream>>>(p, l_first, n_slices, dir, v0, flags);
     CK(cudaGetLastError());
     return DQMCB_OK;
 }

@@ -277,13 +277,15 @@ __device__ void dev_bbar(const Params& p, Work& wk, int walker, int i_stack) {
 }
 
 // propagate_GF_forward: G <- B_l G B_l^-1 (source/dqmc.cpp:113-132).  G in g (ld ldg), scratch t.
+template <bool BIG = true>
 __device__ void dev_wrap_forward(const Params& p, int n, double* g, int ldg, double* t, int ldt, const double* ev, const double* iev) {
-    cta_gemm<false>(t, ldt, p.expK, 1, n, g, 1, ldg, n, nullptr, nullptr);
+    cta_gemm<false, BIG>(t, ldt, p.expK, 1, n, g, 1, ldg, n, nullptr, nullptr);
     __syncthreads();
-    cta_gemm<false>(g, ldg, t, 1, ldt, p.invexpK, 1, n, n, ev, iev);
+    cta_gemm<false, BIG>(g, ldg, t, 1, ldt, p.invexpK, 1, n, n, ev, iev);
     __syncthreads();
 }
 // propagate_GF_backward: G <- B_l^-1 G B_l (source/dqmc.cpp:169-187)
+template <bool BIG = true>
 __device__ void dev_wrap_backward(const Params& p, int n, double* g, int ldg, double* t, int ldt, const double* ev, const double* iev) {
     // t = invexpK (diag(iev) G)   [reference: (invexpK diag(iev)) G — the same product up to rounding order]
     for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
@@ -291,7 +293,7 @@ __device__ void dev_wrap_backward(const Params& p, int n, double* g, int ldg, do
         g[r + (size_t)c * ldg] *= iev[r];
     }
     __syncthreads();
-    cta_gemm<false>(t, ldt, p.invexpK, 1, n, g, 1, ldg, n, nullptr, nullptr);
+    cta_gemm<false, BIG>(t, ldt, p.invexpK, 1, n, g, 1, ldg, n, nullptr, nullptr);
     __syncthreads();
     // g = (t diag(ev)) expK
     for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
@@ -299,7 +301,7 @@ __device__ void dev_wrap_backward(const Params& p, int n, double* g, int ldg, do
         t[r + (size_t)c * ldt] *= ev[c];
     }
     __syncthreads();
-    cta_gemm<false>(g, ldg, t, 1, ldt, p.expK, 1, n, n, nullptr, nullptr);
+    cta_gemm<false, BIG>(g, ldg, t, 1, ldt, p.expK, 1, n, n, nullptr, nullptr);
     __syncthreads();
 }
 
@@ -402,6 +404,7 @@ __device__ int dev_local_update(const Params& p, int n, double* g, int ldg, int8
 // not sit in registers: N = 144 (G in shared memory) and N = 256 (G in L2 / HBM).
 //   dU[m*n + r] = U(r, m),  dV[m*n + c] = V(m, c),  s_diag[n] running diag(G).
 // --------------------------------------------------------------------------------------------------
+template <bool BIG = true>
 __device__ int dev_local_update_delayed(const Params& p, int n, double* g, int ldg, int8_t* s_f, const int* s_perm, const int* s_k,
                                         const double* s_u, double* s_diag, double* dU, double* dV, int K) {
     int accepted = 0, cnt = 0;
@@ -442,14 +445,14 @@ __device__ int dev_local_update_delayed(const Params& p, int n, double* g, int l
             __syncthreads();
             if (threadIdx.x == 0) s_f[i] = (int8_t)newf;
             if (cnt == K) {
-                cta_gemm<true>(g, ldg, dU, 1, n, dV, n, 1, n, nullptr, nullptr, cnt);
+                cta_gemm<true, BIG>(g, ldg, dU, 1, n, dV, n, 1, n, nullptr, nullptr, cnt);
                 cnt = 0;
                 __syncthreads();
             }
         }
     }
     if (cnt) {
-        cta_gemm<true>(g, ldg, dU, 1, n, dV, n, 1, n, nullptr, nullptr, cnt);
+        cta_gemm<true, BIG>(g, ldg, dU, 1, n, dV, n, 1, n, nullptr, nullptr, cnt);
         __syncthreads();
     }
     return accepted;

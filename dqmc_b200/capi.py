@@ -54,7 +54,7 @@ SYMBOLS = [
     "dqmcb_bin_configure", "dqmcb_bin_measure", "dqmcb_bin_fetch", "dqmcb_chi_site_to_chi_r", "dqmcb_chi_r_to_chi_k",
     "dqmcb_pbc_shortest", "dqmcb_sweep_unequal_time", "dqmcb_get_G_unequal", "dqmcb_get_unequal_err",
     "dqmcb_half_wrap_unequal", "dqmcb_measure_unequal_time", "dqmcb_bin_measure_unequal", "dqmcb_bin_fetch_unequal",
-    "dqmcb_set_tape_async", "dqmcb_tape_commit",
+    "dqmcb_set_tape_async", "dqmcb_tape_commit", "dqmcb_to_LDR_noalloc",
 ]
 
 
@@ -94,6 +94,7 @@ def lib():
         L.dqmcb_chi_site_to_chi_r.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, _dp, _dp]
         L.dqmcb_chi_r_to_chi_k.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, _dp, _dp]
         L.dqmcb_pbc_shortest.argtypes = [C.c_int, C.c_int]
+        L.dqmcb_to_LDR_noalloc.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
         L.dqmcb_sweep_unequal_time.argtypes = [C.c_void_p]
         L.dqmcb_get_G_unequal.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp]
         L.dqmcb_get_unequal_err.argtypes = [C.c_void_p, _dp]
@@ -411,6 +412,14 @@ def to_LDR(M, device=0):
     Lo, dO, Ro = np.empty((b, n, n)), np.empty((b, n)), np.empty((b, n, n))
     _ckrc(lib().dqmcb_to_LDR(device, n, b, _d(_cm(M)), _d(Lo), _d(dO), _d(Ro)))
     return _from_cm(Lo), dO, _from_cm(Ro)
+
+
+def to_LDR_noalloc(dM_ptr: int, dL_ptr: int, dd_ptr: int, dR_ptr: int, n: int, batch: int, device=0, stream=0):
+    """dqmcb_to_LDR_noalloc: DEVICE pointers (ints), column-major matrices; asynchronous on `stream`; allocates nothing."""
+    rc = lib().dqmcb_to_LDR_noalloc(device, n, batch, C.c_void_p(dM_ptr), C.c_void_p(dL_ptr), C.c_void_p(dd_ptr), C.c_void_p(dR_ptr),
+                                    C.c_void_p(stream))
+    if rc != OK:
+        raise DqmcbError(rc, lib().dqmcb_last_error(None).decode())
 
 
 def mat_mul_ldr(M, F, device=0):

@@ -1688,6 +1688,87 @@ static int run_ldr_op(int device, int n, int batch, int op, const double* M, con
     return rc;
 }
 
+// ---- allocation-free variant of dqmcb_to_LDR (no counterpart in the reference) ----
+// Scratch of k_ldr_op (the three per-matrix work tiles it keeps in global memory when they do not fit in shared memory,
+// n > ~96, and the failure flag) lives in a file-scope device array instead of a cudaMalloc'ed buffer: usable where the
+// caller may not allocate (CUDA graph capture, serving loops).  Every GPU that loads the library holds these
+// DQMCB_NOALLOC_SCRATCH_BYTES until exit.  All calls share the array: calls that overlap on the GPU race.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[DQMCB_NOALLOC_SCRATCH_BYTES];
+// the array's NAME is a host-side stand-in in host code; its device address is taken once per device, at set-up
+static unsigned char* g_noalloc_ptr[64] = {};
+static size_t g_noalloc_attr[64] = {};  // dynamic shared-memory limit set for k_ldr_op so far
+
+int dqmcb_to_LDR_noalloc(int device, int n, int batch, const double* dM, double* dL, double* dd, double* dR, void* stream) {
+    if (n <= 0 || n > 256 || batch <= 0 || !dM || !dL || !dd || !dR || device < 0 || device >= 64) {
+        g_create_err = "dqmcb_to_LDR_noalloc: bad argument (need 0 < n <= 256, batch > 0, device pointers, 0 <= device < 64)";
+        return DQMCB_EINVAL;
+    }
+    Params p;
+    memset(&p, 0, sizeof(p));
+    p.N = n;
+    p.LD = (n % 2 == 0) ? n + 1 : n;
+    p.W = batch;
+    const size_t tile = (size_t)n * p.LD * 8;
+    const size_t sb = ((small_bytes(n) + 15) & ~(size_t)15);
+    p.smem_mats_stab = (sb + 3 * tile <= (size_t)kMaxSmem) ? 3 : 0;
+    p.smem_stage = (p.smem_mats_stab == 0 && sb + tile <= (size_t)kMaxSmem) ? 1 : 0;
+    const size_t smem = sb + (p.smem_mats_stab + p.smem_stage) * tile;
+    // layout of the static scratch: [0, 256) failure flag, then batch x 3 work tiles (touched only when they are not in SMEM)
+    const size_t need = 256 + (p.smem_mats_stab == 3 ? 0 : (size_t)batch * 3 * tile);
+    if (need > (size_t)DQMCB_NOALLOC_SCRATCH_BYTES) {
+        g_create_err = "dqmcb_to_LDR_noalloc: batch x n needs " + std::to_string(need) + " bytes of scratch, the static array holds " +
+                       std::to_string((size_t)DQMCB_NOALLOC_SCRATCH_BYTES) + " (DQMCB_NOALLOC_SCRATCH_BYTES): split the batch or use dqmcb_to_LDR";
+        return DQMCB_EINVAL;
+    }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        g_create_err = "no CUDA device: dqmc_b200 has no CPU fallback";
+        return DQMCB_ECUDA;
+    }
+    if (device >= ndev || cudaSetDevice(device) != cudaSuccess) {
+        g_create_err = "dqmcb_to_LDR_noalloc: bad device ordinal";
+        return DQMCB_ECUDA;
+    }
+    if (!g_noalloc_ptr[device]) {  // set-up, once per device, with that device current
+        unsigned char* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+        if (e != cudaSuccess || !ptr) {
+            g_create_err = std::string("cudaGetSymbolAddress(g_noalloc_scratch): ") + cudaGetErrorString(e);
+            return DQMCB_ECUDA;
+        }
+        g_noalloc_ptr[device] = ptr;
+    }
+    unsigned char* scratch = g_noalloc_ptr[device];
+    cudaStream_t st = (cudaStream_t)stream;
+    // the array keeps the previous call's contents: the failure flag must start at zero (the tiles are written before read)
+    if (cudaMemsetAsync(scratch, 0, 256, st) != cudaSuccess) {
+        g_create_err = "dqmcb_to_LDR_noalloc: cudaMemsetAsync failed";
+        return DQMCB_ECUDA;
+    }
+    p.fail = reinterpret_cast<int*>(scratch);
+    p.ws = reinterpret_cast<double*>(scratch + 256);
+    LdrArgs a;
+    memset(&a, 0, sizeof(a));
+    a.M = dM;
+    a.Lo = dL;
+    a.dO = dd;
+    a.Ro = dR;
+    if (smem > g_noalloc_attr[device]) {  // raise the opt-in dynamic shared-memory limit of the kernel when this size needs more
+        if (cudaFuncSetAttribute(k_ldr_op, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+            g_create_err = "dqmcb_to_LDR_noalloc: cudaFuncSetAttribute failed";
+            return DQMCB_ECUDA;
+        }
+        g_noalloc_attr[device] = smem;
+    }
+    k_ldr_op<<<batch, kThreads, smem, st>>>(p, 0, a);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        g_create_err = std::string("dqmcb_to_LDR_noalloc launch: ") + cudaGetErrorString(e);
+        return DQMCB_ECUDA;
+    }
+    return DQMCB_OK;  // asynchronous on `stream`; the pivoted QR has no numerical failure mode
+}
+
 int dqmcb_to_LDR(int device, int n, int batch, const double* M, double* L, double* d, double* R) {
     return run_ldr_op(device, n, batch, 0, M, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, L, d, R, nullptr, nullptr);
 }

@@ -202,6 +202,17 @@ int dqmcb_inv_I_plus_ldr(int device, int n, int batch, const double* L, const do
 int dqmcb_inv_I_plus_ldr_mul_ldr(int device, int n, int batch, const double* L1, const double* d1, const double* R1,
                                  const double* L2, const double* d2, const double* R2, double* G);
 
+/* Allocation-free variant of dqmcb_to_LDR.  NO COUNTERPART IN THE REFERENCE: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * dM, dL, dd, dR are DEVICE pointers owned by the caller (batch column-major n x n matrices / n-vectors, as dqmcb_to_LDR);
+ * the kernel's scratch lives in a static device array of DQMCB_NOALLOC_SCRATCH_BYTES that every GPU loading the library
+ * holds until exit.  The call allocates and frees nothing and does not synchronise: it is asynchronous on `stream`
+ * (a cudaStream_t, NULL = default stream).  Limit: 256 + batch * 3 * n * (n + 1 - n % 2) * 8 bytes must fit in the array
+ * for n > ~96 (smaller n keep their work tiles in shared memory: any batch); beyond it DQMCB_EINVAL with a message in
+ * dqmcb_last_error(NULL).  All calls share the one array: calls that overlap on the GPU (different streams) race. */
+#define DQMCB_NOALLOC_SCRATCH_BYTES (8u << 20)
+int dqmcb_to_LDR_noalloc(int device, int n, int batch, const double* dM, double* dL, double* dd, double* dR, void* stream);
+
 /* stablelinalg::inv_invldr_plus_ldr (source/stablelinalg.cpp:160-190; used by the unequal-time sweep) */
 int dqmcb_inv_invldr_plus_ldr(int device, int n, int batch, const double* L1, const double* d1, const double* R1,
                               const double* L2, const double* d2, const double* R2, double* G);

@@ -30,7 +30,7 @@ sys.path.insert(0, ROOT)
 WORKLOADS = {
     # name: (L1, L2, U, t, mu, beta, nt, n_stab, walkers_per_gpu)
     "C1": (8, 8, 4.0, 1.0, 0.0, 8.0, 80, 10, 1024),
-    "C0": (6, 6, 4.0, 1.0, -0.1, 4.0, 40, 10, 1024),
+    "C0": (6, 6, 4.0, 1.0, -0.1, 4.0, 40, 10, 2048),  # 2048 walkers: the LDR stacks (172 MB) exceed the L2
     "C2": (12, 12, 4.0, 1.0, 0.0, 10.0, 100, 10, 296),
     "C3": (16, 16, 6.0, 1.0, 0.0, 16.0, 160, 10, 148),
 }
@@ -46,7 +46,9 @@ def workload_desc(name, wl, n_gpus):
         "lattice": f"{L1}x{L2}", "U": U, "beta": beta, "nt": nt, "n_stab": n_stab,
         "walkers_per_gpu": W, "walkers_total": W * n_gpus,
         "proposals_per_step": 2 * nt * L1 * L2 * W * n_gpus,
-        "l2_policy": "working set (LDR stacks %.0f MB/GPU) larger than the 126 MB L2" % (W * ((nt + n_stab - 1) // n_stab) * (2 * (L1 * L2) ** 2 + L1 * L2) * 8 / 1e6),
+        "l2_policy": (lambda mb: ("working set (LDR stacks %.0f MB/GPU) larger than the 126 MB L2, no flush" % mb) if mb > 126 else
+                      ("WARNING: LDR stacks %.0f MB/GPU fit in the 126 MB L2 and no flush is done -- raise --walkers" % mb))(
+                          W * ((nt + n_stab - 1) // n_stab) * (2 * (L1 * L2) ** 2 + L1 * L2) * 8 / 1e6),
         "parallelism": f"walkers sharded over {n_gpus} GPU(s), no data-path collective",
     }
 
@@ -94,6 +96,28 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(self.samples)}
 
 
+def host_cores():
+    """(hardware threads, physical cores) of this host; physical = distinct (physical id, core id) pairs of /proc/cpuinfo."""
+    threads = os.cpu_count() or 1
+    phys = set()
+    try:
+        pid = cid = None
+        for ln in open("/proc/cpuinfo"):
+            if ln.startswith("physical id"):
+                pid = ln.split(":")[1].strip()
+            elif ln.startswith("core id"):
+                cid = ln.split(":")[1].strip()
+            elif not ln.strip():
+                if cid is not None:
+                    phys.add((pid, cid))
+                pid = cid = None
+        if cid is not None:
+            phys.add((pid, cid))
+    except OSError:
+        pass
+    return threads, (len(phys) or threads)
+
+
 def measured_peaks():
     p = {}
     for fn in ("MEASURED_PEAKS.json", os.path.join("profiles", "fp64_smem_peaks.json")):
@@ -137,7 +161,7 @@ def run_reference_arm(args, wl, name):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    cores = os.cpu_count() or 1
+    cores, phys = host_cores()
     chains = cores
     per_step = {36: 32, 64: 8, 144: 1, 256: 1}.get(wl[0] * wl[1], 1)  # bounded sample: the run ends within minutes
     L1, L2, U, t, mu, beta, nt, n_stab, W = wl
@@ -164,13 +188,17 @@ def run_reference_arm(args, wl, name):
     sweeps = chains * per_step * args.steps
     flips = sweeps * 2 * nt * L1 * L2
     value = flips / secs
-    sample = f"{chains} independent chains (one per host thread) x {per_step} full sweep(s) per step, OpenBLAS pinned to 1 thread per chain"
+    from oracle import ref as _r
+
+    sample = (f"{chains} independent chains (one per hardware thread; {phys} physical cores) x {per_step} full sweep(s) per step -- a bounded sample of "
+              f"the workload, NOT {W} walkers -- reference sources compiled unmodified, {'-O3 -ffast-math' if _r.VARIANT == 'fast' else '-O3'}, "
+              f"OpenBLAS (not MKL: absent here) pinned to 1 thread per chain")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_desc(name, wl, args.gpus),
         "sweeps_per_sec": sweeps / secs,
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": chains, "kind": "reference", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": chains, "physical_cores": phys, "kind": "reference", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -205,17 +233,21 @@ def main():
     _quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=120)  # >= 2 s of timed region at C1
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="C1", choices=list(WORKLOADS))
     ap.add_argument("--walkers", type=int, default=0, help="override walkers per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--therm", type=int, default=100, help="untimed thermalisation sweeps before the timed region (SURVEY 8d: >= 100)")
+    ap.add_argument("--n-stab", type=int, default=0, help="override n_stab (C3 is reported at 10 and at 5, SURVEY H2)")
     ap.add_argument("--delay-k", type=int, default=-1, help="delayed rank-k Metropolis updates (default: 32 for N >= 128, else rank-1)")
     args = ap.parse_args()
     wl = list(WORKLOADS[args.workload])
     if args.walkers:
         wl[8] = args.walkers
+    if args.n_stab:
+        wl[7] = args.n_stab
     wl = tuple(wl)
     if args.impl == "reference":
         run_reference_arm(args, wl, args.workload)
@@ -260,6 +292,13 @@ def main():
         ctx.sweep_0_to_beta()
         ctx.sweep_beta_to_0()
 
+    # ---- thermalisation (untimed): acceptance and the conditioning of the stacks change over the first sweeps
+    t_th = time.perf_counter()
+    for _ in range(args.therm):
+        step()
+    ctx.synchronize()
+    t_th = time.perf_counter() - t_th
+    ctx.reset_stats()
     # ---- kernel-resident throughput (`value`) ----
     # product configuration: walkers split into groups on separate streams (no per-launch events)
     for _ in range(args.warmup):
@@ -346,7 +385,7 @@ def main():
     peaks = measured_peaks()
     dom = int(np.argmax(kms[:2]))
     dom_name = ["propagate (wrap + Metropolis)", "stabilize (Bbar + LDR stack + G)"][dom]
-    acc_rate = float(acc.mean()) / (2.0 * (args.steps + args.warmup)) if acc.size else 0.5  # stats read before the class pass
+    acc_rate = float(acc.mean()) / (2.0 * (args.steps + args.warmup)) if acc.size else 0.5  # stats since the end of thermalisation
     a = min(max(acc_rate, 0.0), 1.0)
     n3 = float(N) ** 3
     # algorithmic FP64 flops per launch: propagate launch = n_stab slices x
@@ -387,12 +426,25 @@ def main():
     cpu_baseline = None
     if not args.no_cpu_baseline:
         try:
-            cores = os.cpu_count() or 1
+            cores, phys = host_cores()
             ns = {36: 160, 64: 40, 144: 4, 256: 1}.get(N, 4)  # ~15-30 CPU-seconds over all host threads
             v, sps, secs = cpu_reference_run(wl, cores, ns, 1)
-            cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "kind": "reference", "sweeps_per_sec": sps,
-                            "sample": f"{cores} independent chains (one per host thread) x {ns} full sweeps of the same model, "
-                                      f"reference sources compiled unmodified (oracle/_ref), OpenBLAS 1 thread/chain, {secs:.1f} s wall"}
+            cpu_baseline = {"value": v, "unit": UNIT, "cores": cores, "physical_cores": phys, "kind": "reference", "sweeps_per_sec": sps,
+                            "sample": f"{cores} independent chains (one per hardware thread; {phys} physical cores) x {ns} full sweeps of the same model "
+                                      f"from a random start (a bounded sample, not {W} walkers), reference sources compiled unmodified (oracle/_ref), -O3, "
+                                      f"OpenBLAS (MKL absent) 1 thread/chain, {secs:.1f} s wall"}
+            # the same sample with the reference's own Release flags (-O3 -ffast-math, CMakeLists.txt:7): separate process,
+            # because the variant is chosen when oracle/ref.py is imported
+            try:
+                env = dict(os.environ, DQMCB_REF_VARIANT="fast")
+                out = subprocess.run([sys.executable, os.path.abspath(__file__), "--impl", "reference", "--workload", args.workload, "--steps", "1",
+                                      "--warmup", "1"] + (["--n-stab", str(args.n_stab)] if args.n_stab else []),
+                                     capture_output=True, text=True, timeout=900, env=env).stdout.strip().splitlines()
+                fl_ = json.loads(out[-1]) if out else {}
+                cpu_baseline["value_fast_math"] = fl_.get("value")
+            except Exception as ex:
+                cpu_baseline["value_fast_math"] = None
+                cpu_baseline["fast_math_note"] = f"unavailable: {ex}"
         except Exception as ex:  # the oracle always exists in-tree; report loudly if the binary is missing
             cpu_baseline = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference", "sample": f"unavailable: {ex}"}
 
@@ -400,7 +452,8 @@ def main():
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic", "config": workload_desc(args.workload, wl, world),
-        "sweeps_per_sec": sweeps_per_sec, "acceptance": a, "max_wrap_err": float(emax.max()),
+        "sweeps_per_sec": sweeps_per_sec, "acceptance": a, "max_wrap_err": float(emax.max()), "mean_wrap_err": float(emean.mean()),
+        "thermalisation": {"sweeps": args.therm, "seconds": t_th, "note": "untimed; acceptance and wrap errors are those of the timed sweeps after it"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(h2d) * world, "d2h_bytes_per_step": int(d2h) * world,
                 "path": "dqmcb_set_tape_async/dqmcb_tape_commit (pinned host RNG tape of the next step uploaded on a copy stream during the current step) + dqmcb_run_sweeps_host (fwd+bwd sweep, measure, fields+observables D2H)"},
         "gpu_launches": int(gpu_launches), "walker_groups": ctx.n_groups(), "delay_k": delay_k,

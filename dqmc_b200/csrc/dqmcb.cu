@@ -30,7 +30,7 @@ using namespace dq;
 // BIG: instantiation for N >= 128 (large-tile tensor-core products, one CTA per SM); the other one keeps its register count
 // for the small lattices, where two CTAs share an SM.
 template <bool BIG>
-__global__ void __launch_bounds__(kThreads) k_propagate(Params p, int l_first, int n_slices, int dir, unsigned long long visit0, int flags) {
+__global__ void __launch_bounds__(kThreads, BIG ? 1 : 2) k_propagate(Params p, int l_first, int n_slices, int dir, unsigned long long visit0, int flags) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int w = blockIdx.x, n = p.N;
     // small arrays
@@ -609,6 +609,53 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
             }
         }
     }
+    p.kg = nullptr;
+    p.kL1 = p.kL2 = 0;
+    {
+        // Generic Kronecker structure: try every factorisation N = L1 L2 (site i = x + L1 y; most balanced first) and
+        // accept the first whose factors Fx = E[(x,0),(x',0)], Fy = E[(0,y),(0,y')] / E[0,0] reproduce exp(-dtau K) AND
+        // exp(+dtau K) to 1e-14 of their largest entry and are symmetric (the right products use the transposed view).
+        const char* nk = getenv("DQMCB_NO_KRON");
+        std::vector<int> cand;
+        for (int a = 1; a <= 16; ++a)
+            if (N % a == 0 && N / a <= 16) cand.push_back(a);
+        std::sort(cand.begin(), cand.end(), [&](int a, int b) { return std::abs(a - N / a) < std::abs(b - N / b) || (std::abs(a - N / a) == std::abs(b - N / b) && a > b); });
+        for (size_t ci = 0; ci < cand.size() && !p.kg && !(nk && nk[0] == (char)49) && expK[0] != 0.0 && invexpK[0] != 0.0; ++ci) {
+            const int L1 = cand[ci], L2 = N / L1;
+            std::vector<double> f(4 * 256, 0.0);
+            bool ok = true;
+            for (int which = 0; which < 2 && ok; ++which) {
+                const double* E = which ? invexpK : expK;
+                double* fx = f.data() + 512 * which;
+                double* fy = fx + 256;
+                for (int b = 0; b < L1; ++b)
+                    for (int a = 0; a < L1; ++a) fx[a + 16 * b] = E[(size_t)a + (size_t)b * N];
+                for (int b = 0; b < L2; ++b)
+                    for (int a = 0; a < L2; ++a) fy[a + 16 * b] = E[(size_t)(L1 * a) + (size_t)(L1 * b) * N] / E[0];
+                double emax = 0.0, dmax = 0.0, smax = 0.0;
+                for (int c = 0; c < N && ok; ++c)
+                    for (int r = 0; r < N; ++r) {
+                        const double e = E[(size_t)r + (size_t)c * N];
+                        const double k = fy[(r / L1) + 16 * (c / L1)] * fx[(r % L1) + 16 * (c % L1)];
+                        emax = std::max(emax, std::fabs(e));
+                        dmax = std::max(dmax, std::fabs(e - k));
+                    }
+                for (int b = 0; b < 16; ++b)
+                    for (int a = 0; a < 16; ++a) {
+                        smax = std::max(smax, std::fabs(fx[a + 16 * b] - fx[b + 16 * a]));
+                        smax = std::max(smax, std::fabs(fy[a + 16 * b] - fy[b + 16 * a]));
+                    }
+                ok = dmax <= 1e-14 * emax && smax <= 1e-14 * emax;
+            }
+            if (ok) {
+                CKC(cudaMalloc(&ctx->d_kg, f.size() * sizeof(double)));
+                CKC(cudaMemcpy(ctx->d_kg, f.data(), f.size() * sizeof(double), cudaMemcpyHostToDevice));
+                p.kg = ctx->d_kg;
+                p.kL1 = L1;
+                p.kL2 = L2;
+            }
+        }
+    }
     CKC(cudaMalloc(&p.fields, (size_t)W * nt * N));
     CKC(cudaMemset(p.fields, 0, (size_t)W * nt * N));
     CKC(cudaMalloc(&p.G, W * nn * 8));
@@ -699,6 +746,7 @@ void dqmcb_destroy(dqmcb_ctx* ctx) {
     cudaFree(ctx->d_expKh);
     cudaFree(ctx->d_invexpKh);
     cudaFree(ctx->d_kron);
+    cudaFree(ctx->d_kg);
     cudaFree(p.fields);
     cudaFree(p.G);
     cudaFree(p.Bbar);
@@ -890,10 +938,9 @@ static int mt_refill(dqmcb_ctx* ctx, int n) {
         ctx->tape_cap = n;
     }
     const size_t smem = (size_t)624 * kMtWalkers * sizeof(uint32_t) + (size_t)p.N * kMtWalkers;
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (!ctx->mt_attr_set) {  // per context (= per device): the attribute belongs to the device the context lives on
         CK(cudaFuncSetAttribute(k_mt_fill, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(624 * kMtWalkers * 4 + 256 * kMtWalkers)));
-        attr_set = true;
+        ctx->mt_attr_set = true;
     }
     k_mt_fill<<<(p.W + kMtWalkers - 1) / kMtWalkers, kMtWalkers, smem, ctx->stream>>>(p.W, p.N, n, ctx->d_mt, ctx->d_tape_perm, ctx->d_tape_k,
                                                                                      ctx->d_tape_u);
@@ -1133,42 +1180,24 @@ static int grouped_sweep(dqmcb_ctx* ctx, int dir) {
             if (p.rng_mode != DQMCB_RNG_TAPE) p.visit_base = 0;
             // visits are consumed in sweep order: slice l is visit (l) forward, (nt-1-l) backward
             const unsigned long long vfirst = v0 + (unsigned long long)((dir > 0) ? l0 : (p0.nt - l1));
-            static const bool dbg = getenv("DQMCB_DEBUG_SYNC") != nullptr;  // development aid: localise a faulting launch
-            static const int gmode = getenv("DQMCB_GROUP_DBG") ? atoi(getenv("DQMCB_GROUP_DBG")) : 0;
-            cudaStream_t gs = (gmode == 2) ? ctx->gstream[0] : ctx->gstream[g];
-            if (gmode == 1 && !(b == 0 && g == 0)) {  // chain the groups: no overlap, no host sync
-                const int pg = (g + ng - 1) % ng;
-                CK(cudaStreamWaitEvent(gs, ctx->gdone[pg], 0));
-            }
-            static cudaEvent_t ev_p[8] = {}, ev_s[8] = {};
-            if ((gmode == 3 || gmode == 4) && !ev_p[0])
-                for (int k = 0; k < 8; ++k) {
-                    cudaEventCreateWithFlags(&ev_p[k], cudaEventDisableTiming);
-                    cudaEventCreateWithFlags(&ev_s[k], cudaEventDisableTiming);
-                }
-            if (gmode == 4 && !(b == 0 && g == 0)) CK(cudaStreamWaitEvent(gs, ev_p[(g + ng - 1) % ng], 0));  // no prop || prop
+            cudaStream_t gs = ctx->gstream[g];
+#ifdef DQMCB_DEBUG_GROUPS  // development aid (compile-time): synchronise after every launch to localise a faulting kernel
+#define DQ_GROUP_CHECK(what)                                                                                                          \
+    do {                                                                                                                              \
+        const cudaError_t e_ = cudaStreamSynchronize(gs);                                                                             \
+        if (e_ != cudaSuccess) {                                                                                                      \
+            fprintf(stderr, "[dqmcb debug] %s failed: %s dir=%d block=%d group=%d w=[%d,%d)\n", what, cudaGetErrorString(e_), dir, i, g, p.w0, p.w1); \
+            return DQMCB_ECUDA;                                                                                                       \
+        }                                                                                                                             \
+    } while (0)
+#else
+#define DQ_GROUP_CHECK(what) do { } while (0)
+#endif
             if (fast64_propagate(ctx, p, (dir > 0) ? l0 : l1 - 1, l1 - l0, dir, vfirst, 3, gs)) return DQMCB_ECUDA;
-            if (gmode == 4) CK(cudaEventRecord(ev_p[g], gs));
-            if (gmode == 3 && !(b == 0 && g == 0)) CK(cudaStreamWaitEvent(gs, ev_s[(g + ng - 1) % ng], 0));  // no stab || stab
-            if (dbg) {
-                const cudaError_t e = cudaStreamSynchronize(ctx->gstream[g]);
-                if (e != cudaSuccess) {
-                    fprintf(stderr, "[dqmcb debug] propagate failed: %s dir=%d block=%d group=%d w=[%d,%d) mode=%d\n", cudaGetErrorString(e), dir, i, g,
-                            p.w0, p.w1, p.rng_mode);
-                    return DQMCB_ECUDA;
-                }
-            }
+            DQ_GROUP_CHECK("propagate");
             fast_stabilize(ctx, (dir > 0) ? l1 - 1 : l0, dir, p.w0, p.w1, gs);
-            if (gmode == 1) CK(cudaEventRecord(ctx->gdone[g], gs));
-            if (gmode == 3) CK(cudaEventRecord(ev_s[g], gs));
-            if (dbg) {
-                const cudaError_t e = cudaStreamSynchronize(ctx->gstream[g]);
-                if (e != cudaSuccess) {
-                    fprintf(stderr, "[dqmcb debug] stabilize failed: %s dir=%d block=%d group=%d w=[%d,%d)\n", cudaGetErrorString(e), dir, i, g, p.w0,
-                            p.w1);
-                    return DQMCB_ECUDA;
-                }
-            }
+            DQ_GROUP_CHECK("stabilize");
+#undef DQ_GROUP_CHECK
             ctx->n_launches += 2;
         }
     }

@@ -29,6 +29,11 @@ struct Params {
     // [0..63] = Ex, [64..127] = Ey, [128..255] the same for exp(+dtau K); null unless N = 64 and the host verified the
     // structure of both to 1e-14 (fast-path Bbar chain and wraps)
     const double* kron;
+    // the same structure for ANY lattice L1 x L2 = N with L1, L2 <= 16 (generic engine: wraps and block products through
+    // cta_kron_apply): four 16 x 16 column-major factor tables [Fx, Fy of exp(-dtau K); Fx, Fy of exp(+dtau K)], verified
+    // by the host to reproduce both matrices to 1e-14 and to be symmetric; null otherwise (dense products)
+    const double* kg;
+    int kL1, kL2;
     int8_t* fields;   // [W][nt][N]
     double* G;        // [W][N*N]   current equal-time Green's function, column-major, ld = N
     double* Bbar;     // [W][N*N]
@@ -77,7 +82,7 @@ struct dqmcb_ctx {
     std::string err;
     bool stacks_ready = false, green_ready = false;
     // owned device allocations
-    double *d_expK = nullptr, *d_invexpK = nullptr, *d_expKh = nullptr, *d_invexpKh = nullptr, *d_kron = nullptr;
+    double *d_expK = nullptr, *d_invexpK = nullptr, *d_expKh = nullptr, *d_invexpKh = nullptr, *d_kron = nullptr, *d_kg = nullptr;
     uint8_t *d_tape_perm = nullptr, *d_tape_k = nullptr;
     double* d_tape_u = nullptr;
     size_t tape_cap = 0;  // visits allocated
@@ -93,6 +98,7 @@ struct dqmcb_ctx {
     double* d_obs = nullptr;  // [W][4]
     double* d_scratchNN = nullptr;  // [W][N*N] for measurement outputs
     uint32_t* d_mt = nullptr;       // [W][625] mt19937 state + index (MT19937 mode)
+    bool mt_attr_set = false;       // k_mt_fill's dynamic shared-memory limit raised on this context's device
     // measurement bin on the device (dqmcb_bin_*): per-walker vectors and the running sums
     int bin_L1 = 0, bin_L2 = 0;
     double* d_binpart = nullptr;    // [W][3 + N]

@@ -207,9 +207,14 @@ __device__ void dev_inv_I_plus_ldr_mul_ldr(const Params& p, Work& wk, int n, con
     cta_lu(f0, lf0, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
     DQ_PH(p, 6);
     note_fail(p, wk, 12);
-    set_diag(b1, l1, n, wk.sv[2]);
+    // right-hand side D2_large^-1 written with its rows already interchanged: (P D)(i, c) = D(perm[i], c)
+    cta_perm_from_ipiv(wk.ipiv, wk.jpvt, n);
+    for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
+        const int r = e % n, c = e / n;
+        b1[r + (size_t)c * l1] = (wk.jpvt[r] == c) ? wk.sv[2][c] : 0.0;
+    }
     __syncthreads();
-    cta_lu_solve(f0, lf0, n, wk.ipiv, b1, 1, l1);  // X = R2^-1 D2_large^-1
+    cta_lu_solve(f0, lf0, n, wk.ipiv, b1, 1, l1, true);  // X = R2^-1 D2_large^-1
     __syncthreads();
     DQ_PH(p, 7);
     // TermA = D1l^-1 (L1^T X)
@@ -220,13 +225,6 @@ __device__ void dev_inv_I_plus_ldr_mul_ldr(const Params& p, Work& wk, int n, con
     // M = TermA + D1s (R1 (L2 D2s))
     cta_gemm<true>(b2, l2, R1, 1, ldg, b0, 1, l0, n, wk.sv[1], nullptr);
     __syncthreads();
-    // RHS = D1l^-1 L1^T  -> b0      (rhs_mode 1: RHS = D1s R1, stablelinalg::inv_invldr_plus_ldr,
-    //                                  source/stablelinalg.cpp:160-190 -- same M, different right-hand side)
-    for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
-        const int r = e % n, c = e / n;
-        b0[r + (size_t)c * l0] = rhs_mode ? wk.sv[1][r] * R1[r + (size_t)c * ldg] : wk.sv[0][r] * L1[c + (size_t)r * ldg];
-    }
-    __syncthreads();
     double* f2 = b2;
     int lf2 = l2;
     stage_in(wk, n, f2, lf2);
@@ -234,7 +232,17 @@ __device__ void dev_inv_I_plus_ldr_mul_ldr(const Params& p, Work& wk, int n, con
     cta_lu(f2, lf2, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
     DQ_PH(p, 10);
     note_fail(p, wk, 13);
-    cta_lu_solve(f2, lf2, n, wk.ipiv, b0, 1, l0);  // Y = M^-1 RHS
+    // RHS = D1l^-1 L1^T  -> b0      (rhs_mode 1: RHS = D1s R1, stablelinalg::inv_invldr_plus_ldr,
+    //                                  source/stablelinalg.cpp:160-190 -- same M, different right-hand side),
+    // built after the factorisation so that it can be written with its rows already interchanged
+    cta_perm_from_ipiv(wk.ipiv, wk.jpvt, n);
+    for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
+        const int r = e % n, c = e / n;
+        const int pr = wk.jpvt[r];
+        b0[r + (size_t)c * l0] = rhs_mode ? wk.sv[1][pr] * R1[pr + (size_t)c * ldg] : wk.sv[0][pr] * L1[c + (size_t)pr * ldg];
+    }
+    __syncthreads();
+    cta_lu_solve(f2, lf2, n, wk.ipiv, b0, 1, l0, true);  // Y = M^-1 RHS
     __syncthreads();
     DQ_PH(p, 11);
     cta_gemm<false>(b2, l2, b1, 1, l1, b0, 1, l0, n, nullptr, nullptr);  // G = X Y
@@ -251,6 +259,21 @@ __device__ void dev_bbar(const Params& p, Work& wk, int walker, int i_stack) {
     const int l0 = i_stack * p.n_stab;
     const int l1 = min(l0 + p.n_stab, p.nt);
     const int8_t* f = p.fields + ((size_t)walker * p.nt) * n;
+    if (p.kg) {
+        // Kronecker chain in place in b[0]: B_l X = diag(ev_l) (Fy (x) Fx) X, the scaling read straight from the field
+        // values; a warp keeps its column groups for the whole chain, so no block barrier between the slices
+        double* X = wk.b[0];
+        const int ldx = wk.ld[0];
+        __syncthreads();
+        for (int e = threadIdx.x; e < n * n; e += blockDim.x) {  // B_{l0} = diag(ev) expK
+            const int r = e % n, c = e / n;
+            X[r + (size_t)c * ldx] = p.lut_ev[f[(size_t)l0 * n + r]] * p.expK[e];
+        }
+        __syncthreads();
+        for (int l = l0 + 1; l < l1; ++l)
+            cta_kron_apply<false>(X, 1, ldx, n, p.kL1, p.kL2, p.kg, p.kg + 256, nullptr, nullptr, f + (size_t)l * n, p.lut_ev);
+        return;
+    }
     double* cur = ((l1 - l0) & 1) ? wk.b[0] : wk.b[1];  // so that the last product lands in b[0]
     double* oth = ((l1 - l0) & 1) ? wk.b[1] : wk.b[0];
     const int ldc = ((l1 - l0) & 1) ? wk.ld[0] : wk.ld[1];
@@ -279,6 +302,13 @@ __device__ void dev_bbar(const Params& p, Work& wk, int walker, int i_stack) {
 // propagate_GF_forward: G <- B_l G B_l^-1 (source/dqmc.cpp:113-132).  G in g (ld ldg), scratch t.
 template <bool BIG = true>
 __device__ void dev_wrap_forward(const Params& p, int n, double* g, int ldg, double* t, int ldt, const double* ev, const double* iev) {
+    if (p.kg) {  // G <- diag(ev) (E G) : left product;  then (.) Ei diag(iev) : left product on the transposed view
+        cta_kron_apply<false, BIG ? 4 : 2>(g, 1, ldg, n, p.kL1, p.kL2, p.kg, p.kg + 256, nullptr, ev, nullptr, nullptr);
+        __syncthreads();
+        cta_kron_apply<true, BIG ? 4 : 2>(g, ldg, 1, n, p.kL1, p.kL2, p.kg + 512, p.kg + 768, nullptr, iev, nullptr, nullptr);
+        __syncthreads();
+        return;
+    }
     cta_gemm<false, BIG>(t, ldt, p.expK, 1, n, g, 1, ldg, n, nullptr, nullptr);
     __syncthreads();
     cta_gemm<false, BIG>(g, ldg, t, 1, ldt, p.invexpK, 1, n, n, ev, iev);
@@ -287,6 +317,13 @@ __device__ void dev_wrap_forward(const Params& p, int n, double* g, int ldg, dou
 // propagate_GF_backward: G <- B_l^-1 G B_l (source/dqmc.cpp:169-187)
 template <bool BIG = true>
 __device__ void dev_wrap_backward(const Params& p, int n, double* g, int ldg, double* t, int ldt, const double* ev, const double* iev) {
+    if (p.kg) {  // G <- Ei (diag(iev) G) : left product with pre-scaling;  then (. diag(ev)) E on the transposed view
+        cta_kron_apply<false, BIG ? 4 : 2>(g, 1, ldg, n, p.kL1, p.kL2, p.kg + 512, p.kg + 768, iev, nullptr, nullptr, nullptr);
+        __syncthreads();
+        cta_kron_apply<true, BIG ? 4 : 2>(g, ldg, 1, n, p.kL1, p.kL2, p.kg, p.kg + 256, ev, nullptr, nullptr, nullptr);
+        __syncthreads();
+        return;
+    }
     // t = invexpK (diag(iev) G)   [reference: (invexpK diag(iev)) G — the same product up to rounding order]
     for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
         const int r = e % n, c = e / n;

@@ -14,7 +14,10 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "_ref", "libdqmc_ref.so")
+# DQMCB_REF_VARIANT=fast selects the build with the reference's own Release flags (-O3 -ffast-math, CMakeLists.txt:7;
+# `make -C oracle FAST=1` -> oracle/_ref_fast/): used by bench.py to report the CPU arm both ways
+VARIANT = "fast" if os.environ.get("DQMCB_REF_VARIANT", "") == "fast" else "O3"
+LIB_PATH = os.path.join(_HERE, "_ref_fast" if VARIANT == "fast" else "_ref", "libdqmc_ref.so")
 _lib = None
 
 _dp = C.POINTER(C.c_double)
@@ -29,6 +32,7 @@ def build(reference_root: str = "/root/reference", force: bool = False) -> bool:
     if force:
         subprocess.check_call(["make", "-C", _HERE, "clean"], stdout=subprocess.DEVNULL)
     subprocess.check_call(["make", "-C", _HERE, f"REF={reference_root}"], stdout=subprocess.DEVNULL)  # incremental
+    subprocess.check_call(["make", "-C", _HERE, f"REF={reference_root}", "FAST=1"], stdout=subprocess.DEVNULL)
     return os.path.exists(LIB_PATH)
 
 

@@ -260,8 +260,8 @@ __device__ void dev_bbar(const Params& p, Work& wk, int walker, int i_stack) {
     const int l1 = min(l0 + p.n_stab, p.nt);
     const int8_t* f = p.fields + ((size_t)walker * p.nt) * n;
     if (p.kg) {
-        // Kronecker chain in place in b[0]: B_l X = diag(ev_l) (Fy (x) Fx) X, the scaling read straight from the field
-        // values; a warp keeps its column groups for the whole chain, so no block barrier between the slices
+        // Kronecker chain in place in b[0]: B_l X = diag(ev_l) (Fy (x) Fx) X; a warp keeps its column groups for the whole
+        // chain, so the slices need no barrier for the matrix itself
         double* X = wk.b[0];
         const int ldx = wk.ld[0];
         __syncthreads();
@@ -270,8 +270,13 @@ __device__ void dev_bbar(const Params& p, Work& wk, int walker, int i_stack) {
             X[r + (size_t)c * ldx] = p.lut_ev[f[(size_t)l0 * n + r]] * p.expK[e];
         }
         __syncthreads();
-        for (int l = l0 + 1; l < l1; ++l)
-            cta_kron_apply<false>(X, 1, ldx, n, p.kL1, p.kL2, p.kg, p.kg + 256, nullptr, nullptr, f + (size_t)l * n, p.lut_ev);
+        // the slice's scaling exp(g eta) is staged in shared memory, double buffered: ONE block barrier per slice
+        for (int l = l0 + 1; l < l1; ++l) {
+            double* ev = wk.sv[l & 1];
+            for (int i = threadIdx.x; i < n; i += blockDim.x) ev[i] = p.lut_ev[f[(size_t)l * n + i]];
+            __syncthreads();
+            cta_kron<false, 4>(X, ldx, n, p.kL1, p.kL2, p.kg, p.kg + 256, nullptr, ev);
+        }
         return;
     }
     double* cur = ((l1 - l0) & 1) ? wk.b[0] : wk.b[1];  // so that the last product lands in b[0]
@@ -303,9 +308,9 @@ __device__ void dev_bbar(const Params& p, Work& wk, int walker, int i_stack) {
 template <bool BIG = true>
 __device__ void dev_wrap_forward(const Params& p, int n, double* g, int ldg, double* t, int ldt, const double* ev, const double* iev) {
     if (p.kg) {  // G <- diag(ev) (E G) : left product;  then (.) Ei diag(iev) : left product on the transposed view
-        cta_kron_apply<false, BIG ? 4 : 2>(g, 1, ldg, n, p.kL1, p.kL2, p.kg, p.kg + 256, nullptr, ev, nullptr, nullptr);
+        cta_kron<false, BIG ? 4 : 2>(g, ldg, n, p.kL1, p.kL2, p.kg, p.kg + 256, nullptr, ev);
         __syncthreads();
-        cta_kron_apply<true, BIG ? 4 : 2>(g, ldg, 1, n, p.kL1, p.kL2, p.kg + 512, p.kg + 768, nullptr, iev, nullptr, nullptr);
+        cta_kron<true, BIG ? 4 : 2>(g, ldg, n, p.kL1, p.kL2, p.kg + 512, p.kg + 768, nullptr, iev);
         __syncthreads();
         return;
     }
@@ -318,9 +323,9 @@ __device__ void dev_wrap_forward(const Params& p, int n, double* g, int ldg, dou
 template <bool BIG = true>
 __device__ void dev_wrap_backward(const Params& p, int n, double* g, int ldg, double* t, int ldt, const double* ev, const double* iev) {
     if (p.kg) {  // G <- Ei (diag(iev) G) : left product with pre-scaling;  then (. diag(ev)) E on the transposed view
-        cta_kron_apply<false, BIG ? 4 : 2>(g, 1, ldg, n, p.kL1, p.kL2, p.kg + 512, p.kg + 768, iev, nullptr, nullptr, nullptr);
+        cta_kron<false, BIG ? 4 : 2>(g, ldg, n, p.kL1, p.kL2, p.kg + 512, p.kg + 768, iev, nullptr);
         __syncthreads();
-        cta_kron_apply<true, BIG ? 4 : 2>(g, ldg, 1, n, p.kL1, p.kL2, p.kg, p.kg + 256, ev, nullptr, nullptr, nullptr);
+        cta_kron<true, BIG ? 4 : 2>(g, ldg, n, p.kL1, p.kL2, p.kg, p.kg + 256, ev, nullptr);
         __syncthreads();
         return;
     }

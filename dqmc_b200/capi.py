@@ -15,7 +15,7 @@ LIB_PATH = os.path.join(_HERE, "libdqmc_b200.so")
 
 OK, EINVAL, ECUDA, ENUMERIC, ESTATE = 0, 1, 2, 3, 4
 RNG_TAPE, RNG_PHILOX, RNG_MT19937 = 0, 1, 2
-PTR_FIELDS, PTR_G, PTR_LOGDET, PTR_OBS = 0, 1, 2, 3
+PTR_FIELDS, PTR_G, PTR_LOGDET, PTR_OBS, PTR_STACK_L, PTR_STACK_D, PTR_STACK_R = 0, 1, 2, 3, 4, 5, 6
 
 
 class Config(C.Structure):

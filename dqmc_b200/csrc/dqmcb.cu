@@ -1329,6 +1329,9 @@ void* dqmcb_device_ptr(dqmcb_ctx* ctx, int which) {
         case DQMCB_PTR_G: return ctx->p.G;
         case DQMCB_PTR_LOGDET: return ctx->p.logdet;
         case DQMCB_PTR_OBS: return ctx->d_obs;
+        case DQMCB_PTR_STACK_L: return ctx->p.stackL;
+        case DQMCB_PTR_STACK_D: return ctx->p.stackD;
+        case DQMCB_PTR_STACK_R: return ctx->p.stackR;
         default: return nullptr;
     }
 }

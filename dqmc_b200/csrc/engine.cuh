@@ -100,19 +100,23 @@ __device__ inline void stage_in(Work& wk, int n, double*& F, int& ldf) {
 __device__ void dev_to_ldr(Work& wk, int n, double* A, int lda, double* Qo, int ldq, double* Ro, int ldr, double* dout) {
     __syncthreads();
     stage_in(wk, n, A, lda);
-    cta_qrp(A, lda, n, wk.tau, wk.jpvt, wk.vn1, wk.vn2);
+    int* list = reinterpret_cast<int*>(wk.jrow);  // n doubles = 2 n ints: active-column list and its inverse map
+    cta_qrp(A, lda, n, wk.tau, wk.jpvt, wk.vn1, wk.vn2, list, list + n);
+    // column jpvt[j] of A holds R(0..j, j) (and the reflector below): d_j = |R(j,j)|, and R_final = (D^-1 R) P^T puts
+    // that column back at index jpvt[j] -- where it already is
     for (int j = threadIdx.x; j < n; j += blockDim.x) {
-        const double dj = fabs(A[j + (size_t)j * lda]);
+        const int c = wk.jpvt[j];
+        const double dj = fabs(A[j + (size_t)c * lda]);
         dout[j] = dj;
         wk.vn1[j] = 1.0 / dj;  // D_inv_vec (vn1 is free after the factorisation)
+        wk.ipiv[c] = j;        // step at which column c was chosen (scratch)
     }
     __syncthreads();
     for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
-        const int i = e % n, j = e / n;
-        const double v = (i <= j) ? wk.vn1[i] * A[i + (size_t)j * lda] : 0.0;
-        Ro[i + (size_t)wk.jpvt[j] * ldr] = v;  // R_final = R_normalized.cols(P_inv)
+        const int i = e % n, c = e / n;
+        Ro[i + (size_t)c * ldr] = (i <= wk.ipiv[c]) ? wk.vn1[i] * A[i + (size_t)c * lda] : 0.0;
     }
-    cta_form_q(Qo, ldq, A, lda, wk.tau, n);
+    cta_form_q(Qo, ldq, A, lda, wk.tau, n, wk.jpvt);
     __syncthreads();
 }
 

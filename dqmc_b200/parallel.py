@@ -56,8 +56,15 @@ class ContextEngine:
         from . import capi
 
         self.ctx, self.capi, self.device = ctx, capi, device
+        dev = torch.device("cuda", device)
         ptr = ctx.device_ptr(capi.PTR_FIELDS)
-        self._fields = torch.as_tensor(_DevPtr(ptr, (ctx.W, ctx.nt, ctx.N), "|i1"), device=torch.device("cuda", device))
+        self._fields = torch.as_tensor(_DevPtr(ptr, (ctx.W, ctx.nt, ctx.N), "|i1"), device=dev)
+        # the rest of a walker's state (LDR stack, G, log det M): zero-copy views for snapshot / restore around an exchange
+        W, N, ns = ctx.W, ctx.N, ctx.n_stack
+        view = lambda which, shape: torch.as_tensor(_DevPtr(ctx.device_ptr(which), shape, "<f8"), device=dev)
+        self._state = [view(capi.PTR_STACK_L, (W, ns * N * N)), view(capi.PTR_STACK_D, (W, ns * N)), view(capi.PTR_STACK_R, (W, ns * N * N)),
+                       view(capi.PTR_G, (W, N * N)), view(capi.PTR_LOGDET, (W,))]
+        self._snap = None
 
     @property
     def n_walkers(self):
@@ -71,6 +78,23 @@ class ContextEngine:
     def install_fields(self, t: torch.Tensor) -> None:
         if t.data_ptr() != self._fields.data_ptr():
             self._fields.copy_(t)
+        torch.cuda.synchronize(self.device)
+
+    def snapshot(self) -> None:
+        """Device-side copy of every walker's derived state (stacks, G, log det M) -- 0.5 GB at C1 / 1024 walkers, a
+        fraction of a millisecond of HBM time against the ~50 ms of a rebuild."""
+        self.ctx.synchronize()
+        if self._snap is None:
+            self._snap = [torch.empty_like(t) for t in self._state]
+        for d, s_ in zip(self._snap, self._state):
+            d.copy_(s_)
+
+    def restore(self, walkers: torch.Tensor) -> None:
+        """Put the snapshot back for the walkers selected by the bool mask `walkers` (their exchange was rejected)."""
+        idx = torch.nonzero(walkers.to(self._fields.device), as_tuple=False).flatten()
+        if idx.numel():
+            for d, s_ in zip(self._state, self._snap):
+                d.index_copy_(0, idx, s_.index_select(0, idx))
         torch.cuda.synchronize(self.device)
 
     def rebuild(self) -> None:
@@ -92,6 +116,7 @@ class ReplicaExchange:
         self.proposed = 0
         self.comm_device = comm_device  # where scalars travel (cuda for nccl, cpu for gloo)
         self._gen = np.random.default_rng(seed * 7919 + rank)
+        self.profile = None       # set to a dict to collect per-phase wall times of step() (development aid; adds syncs)
 
     def _p2p(self, send: torch.Tensor, recv: torch.Tensor, partner: int):
         ops = [dist.P2POp(dist.isend, send, partner, self.group), dist.P2POp(dist.irecv, recv, partner, self.group)]
@@ -107,16 +132,34 @@ class ReplicaExchange:
         self.attempt += 1
         partner = partner_rank(self.rank, self.ws, self.attempt)
         W = self.e.n_walkers
+        import time as _time
+
+        _t = [_time.perf_counter()]
+
+        def _mark(name):
+            if self.profile is not None:
+                if torch.cuda.is_available():
+                    torch.cuda.synchronize()
+                now = _time.perf_counter()
+                self.profile[name] = self.profile.get(name, 0.0) + now - _t[0]
+                _t[0] = now
+
         if partner == self.rank or partner < 0 or partner >= self.ws:
             return np.zeros(W, dtype=bool)
         own = self.e.fields_buffer()
         mine = own.clone()
         theirs = torch.empty_like(own)
         self._p2p(mine, theirs, partner)                      # MPI_Sendrecv of the fields (update.cpp:64-66)
+        _mark("swap_fields")
         S_own = self.e.global_action().to(torch.float64)      # S_r({s}_r)          (update.cpp:73)
+        can_snapshot = hasattr(self.e, "snapshot")
+        if can_snapshot:
+            self.e.snapshot()                                 # own stacks / G / log det M, in case the swap is rejected
+        _mark("own_action_snapshot")
         self.e.install_fields(theirs)
         self.e.rebuild()                                      # stacks + G from scratch (update.cpp:76-80)
         S_cross = self.e.global_action().to(torch.float64)    # S_r({s}_partner)    (update.cpp:81)
+        _mark("rebuild_cross_action")
         dev = self.comm_device if self.comm_device is not None else own.device
         pack = torch.stack([S_cross, S_own]).to(dev)          # both scalars in one message (update.cpp:84-90)
         other = torch.empty_like(pack)
@@ -134,12 +177,20 @@ class ReplicaExchange:
             for r in dist.batch_isend_irecv([dist.P2POp(dist.irecv, verdict, partner, self.group)]):
                 r.wait()
             acc = verdict.cpu().numpy().astype(bool)
+        _mark("actions_verdict")
         self.proposed += W
         self.accepted += int(acc.sum())
         if not acc.all():                                     # restore rejected walkers (update.cpp:109-115)
             keep = torch.from_numpy(acc).to(own.device).view(W, 1, 1)
             self.e.install_fields(torch.where(keep, theirs, mine))
-            self.e.rebuild()
+            if can_snapshot:
+                # the reference rebuilds stacks and G from the restored fields (init_stacks + init_greenfunctions, a pure
+                # function of the fields); the state saved before the swap IS that result, so the rejected walkers get it
+                # back by a masked device copy and nothing is recomputed
+                self.e.restore(torch.from_numpy(~acc))
+            else:
+                self.e.rebuild()
+        _mark("restore_rejected")
         return acc
 
 

@@ -129,6 +129,9 @@ int dqmcb_reset_stats(dqmcb_ctx* ctx);
 #define DQMCB_PTR_G 1
 #define DQMCB_PTR_LOGDET 2
 #define DQMCB_PTR_OBS 3
+#define DQMCB_PTR_STACK_L 4 /* f64 [W][n_stack][N*N]: LDRStack factors L (include/stackngf.h:34-77), for device-side snapshots */
+#define DQMCB_PTR_STACK_D 5 /* f64 [W][n_stack][N] */
+#define DQMCB_PTR_STACK_R 6 /* f64 [W][n_stack][N*N] */
 void* dqmcb_device_ptr(dqmcb_ctx* ctx, int which);
 
 /* ---- measurements / action ------------------------------------------------------------------------ */

@@ -54,7 +54,7 @@ SYMBOLS = [
     "dqmcb_bin_configure", "dqmcb_bin_measure", "dqmcb_bin_fetch", "dqmcb_chi_site_to_chi_r", "dqmcb_chi_r_to_chi_k",
     "dqmcb_pbc_shortest", "dqmcb_sweep_unequal_time", "dqmcb_get_G_unequal", "dqmcb_get_unequal_err",
     "dqmcb_half_wrap_unequal", "dqmcb_measure_unequal_time", "dqmcb_bin_measure_unequal", "dqmcb_bin_fetch_unequal",
-    "dqmcb_set_tape_async", "dqmcb_tape_commit", "dqmcb_to_LDR_noalloc",
+    "dqmcb_set_tape_async", "dqmcb_tape_commit", "dqmcb_to_LDR_noalloc", "dqmcb_measure_kinetic_spin",
 ]
 
 
@@ -95,6 +95,7 @@ def lib():
         L.dqmcb_chi_r_to_chi_k.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, _dp, _dp]
         L.dqmcb_pbc_shortest.argtypes = [C.c_int, C.c_int]
         L.dqmcb_to_LDR_noalloc.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.dqmcb_measure_kinetic_spin.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double, _dp, _dp]
         L.dqmcb_sweep_unequal_time.argtypes = [C.c_void_p]
         L.dqmcb_get_G_unequal.argtypes = [C.c_void_p, C.c_int, C.c_int, _dp]
         L.dqmcb_get_unequal_err.argtypes = [C.c_void_p, _dp]
@@ -310,6 +311,13 @@ class Context:
         self._ck(self.L.dqmcb_measure_equal_time(self.h, _d(sc), _d(corr)))
         return sc, (_from_cm(corr) if want_corr else None)
 
+    def measure_kinetic_spin(self, L1: int, L2: int, t: float = 1.0):
+        """(ekin[W], szz_r[W, L1, L2]): kinetic energy per site and (1/N) sum_i <Sz_i Sz_{i+(dx,dy)}> of every walker
+        (no reference counterpart; see include/dqmc_b200.h)."""
+        e, s = np.empty(self.W), np.empty((self.W, L1 * L2))
+        self._ck(self.L.dqmcb_measure_kinetic_spin(self.h, L1, L2, float(t), _d(e), _d(s)))
+        return e, s.reshape((self.W, L2, L1)).transpose(0, 2, 1)  # [w, dx, dy]
+
     def bin_configure(self, L1: int, L2: int) -> None:
         self._ck(self.L.dqmcb_bin_configure(self.h, L1, L2))
         self._bin_shape = (L1, L2)
@@ -412,6 +420,11 @@ def to_LDR(M, device=0):
     Lo, dO, Ro = np.empty((b, n, n)), np.empty((b, n)), np.empty((b, n, n))
     _ckrc(lib().dqmcb_to_LDR(device, n, b, _d(_cm(M)), _d(Lo), _d(dO), _d(Ro)))
     return _from_cm(Lo), dO, _from_cm(Ro)
+
+
+def spin_structure_factor(szz_r: np.ndarray) -> np.ndarray:
+    """S(q) on the grid q = 2 pi (n / L1, m / L2) from szz_r[..., dx, dy]: S(q) = sum_r cos(q.r) szz_r (real part of the DFT)."""
+    return np.real(np.fft.fft2(szz_r, axes=(-2, -1)))
 
 
 def to_LDR_noalloc(dM_ptr: int, dL_ptr: int, dd_ptr: int, dR_ptr: int, n: int, batch: int, device=0, stream=0):

@@ -1354,6 +1354,27 @@ int dqmcb_measure_equal_time(dqmcb_ctx* ctx, double* scalars, double* corr) {
     if (corr) CK(cudaMemcpy(corr, ctx->d_scratchNN, (size_t)p.W * p.N * p.N * 8, cudaMemcpyDeviceToHost));
     return DQMCB_OK;
 }
+// kinetic energy per site and displacement-folded Sz-Sz correlation of every walker (no reference counterpart: measure.cuh)
+int dqmcb_measure_kinetic_spin(dqmcb_ctx* ctx, int L1, int L2, double t, double* ekin, double* szz_r) {
+    NEED(ctx);
+    const Params& p = ctx->p;
+    if (L1 <= 0 || L2 <= 0 || L1 * L2 != p.N || !ekin || !szz_r) {
+        ctx->err = "dqmcb_measure_kinetic_spin: L1*L2 must equal n_sites; outputs must not be null";
+        return DQMCB_EINVAL;
+    }
+    double* d_e = ctx->d_obs;           // [W] of the [W][4] scalar scratch
+    double* d_s = ctx->d_scratchNN;     // [W][N] of the [W][N*N] matrix scratch
+    {
+        TimeScope ts(ctx, DQMCB_K_OTHER);
+        ctx->n_launches += 1;
+        k_kinetic_spin<<<p.W, kThreads, 0, ctx->stream>>>(p, L1, L2, t, d_e, d_s);
+    }
+    CK(cudaGetLastError());
+    CK(cudaMemcpyAsync(ekin, d_e, (size_t)p.W * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(szz_r, d_s, (size_t)p.W * p.N * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return DQMCB_OK;
+}
 // ---- measurement bins (include/measurementh5.h:189-274) -----------------------------------------------
 int dqmcb_bin_configure(dqmcb_ctx* ctx, int L1, int L2) {
     NEED(ctx);

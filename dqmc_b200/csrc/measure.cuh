@@ -137,4 +137,38 @@ __global__ void k_chi_r_to_chi_k(int L1, int L2, const double* __restrict__ chi_
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Kinetic energy and spin correlation (north_star's correctness clause names them; the reference has NO code for either:
+// source/model.cpp:167-288 stops at density / double occupancy / s-wave / density correlation).  Per HS configuration the
+// two spin species share G (attractive model, charge-channel decoupling), <c+_i c_j> = delta_ij - G(j, i), so by Wick:
+//   E_kin / N = (2 t / N) sum_i sum_{d in {+x, +y}} [ G(i + d, i) + G(i, i + d) ]          (both spins, PBC, site x + L1 y)
+//   <Sz_i Sz_j> = (1/2) (delta_ij - G(j, i)) G(i, j)
+//   szz_r(dx, dy) = (1/N) sum_i <Sz_i Sz_{i + (dx, dy)}>          (displacement fold; S(q) = sum_r cos(q r) szz_r on the host)
+// One CTA per walker; thread r owns displacement r and sums over the N origins (deterministic, no atomics).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) k_kinetic_spin(Params p, int L1, int L2, double t, double* __restrict__ ekin /*[W]*/,
+                                                           double* __restrict__ szz /*[W][N]*/) {
+    __shared__ double red[64];
+    const int w = blockIdx.x, n = p.N;
+    const double* G = p.G + (size_t)w * n * n;
+    double part = 0.0;
+    for (int i = threadIdx.x; i < n; i += blockDim.x) {
+        const int x = i % L1, y = i / L1;
+        const int jx = (x + 1) % L1 + L1 * y, jy = x + L1 * ((y + 1) % L2);
+        part += G[jx + (size_t)i * n] + G[i + (size_t)jx * n] + G[jy + (size_t)i * n] + G[i + (size_t)jy * n];
+    }
+    const double tot = cta_reduce_sum(part, red);
+    if (threadIdx.x == 0) ekin[w] = 2.0 * t * tot / n;
+    for (int r = threadIdx.x; r < n; r += blockDim.x) {
+        const int dx = r % L1, dy = r / L1;
+        double s = 0.0;
+        for (int i = 0; i < n; ++i) {
+            const int x = i % L1, y = i / L1;
+            const int j = (x + dx) % L1 + L1 * ((y + dy) % L2);
+            s += 0.5 * (((i == j) ? 1.0 : 0.0) - G[j + (size_t)i * n]) * G[i + (size_t)j * n];
+        }
+        szz[(size_t)w * n + r] = s / n;
+    }
+}
+
 }  // namespace dq

@@ -81,28 +81,64 @@ def main(argv=None) -> dict:
         beta, exchange_step = betas[rank], p.getInt("ParallelTempering", "sweep_steps")
     else:
         beta, exchange_step = p.getDouble("simulation", "beta"), 0
-    seed = (int(time.time()) if args.seed is None else args.seed) + rank
+    # time-based default seed (source/main.cpp:37): taken ONCE, on rank 0, and broadcast -- ranks that start a second apart
+    # would otherwise draw the same seed + rank and run duplicate chains
+    seed0 = int(time.time()) if args.seed is None else args.seed
+    if dist is not None and args.seed is None:
+        import torch
+
+        tsd = torch.tensor([seed0], dtype=torch.int64, device="cuda")
+        dist.broadcast(tsd, src=0)
+        seed0 = int(tsd.item())
+    seed = seed0 + rank
     N = L1 * L2
-    delay_k = args.delay_k if args.delay_k >= 0 else (32 if N >= 128 else 0)
+    delay_k = args.delay_k if args.delay_k >= 0 else (0 if N < 128 else (16 if N <= 160 else 32))
+    if unequal:
+        # the unequal-time sweep keeps Gtt / Gt0 / G0t of every slice of every walker on the device: fail BEFORE thermalisation,
+        # naming the walker count that fits, instead of with a bare cudaMalloc error in the first bin
+        import torch
+
+        need = args.walkers * 3 * (nt + 1) * N * N * 8
+        free = torch.cuda.mem_get_info(local)[0] if torch.cuda.is_available() else 0
+        if free and need > 0.9 * free:
+            fit = int(0.9 * free // (3 * (nt + 1) * N * N * 8))
+            sys.stderr.write(f"ERROR: isMeasureUnequalTime needs {need / 1e9:.1f} GB of device memory for {args.walkers} walkers "
+                             f"({free / 1e9:.1f} GB free): use --walkers {fit} or fewer\n")
+            raise SystemExit(1)
     model = host.AttractiveHubbard(L1, L2, U, t, mu, beta, nt, n_stab, args.walkers, device=local, delay_k=delay_k)
     ctx = model.ctx
     ckpt = os.path.join(args.out, f"checkpoint_{rank}.npz")
     mm = measure.MeasurementManager(ctx, L1, L2, rank=rank, out_dir=args.out, device=local, unequal_time=unequal)
     start_bin, therm_done = 0, False
-    if args.resume and os.path.exists(ckpt):
+    have = int(args.resume and os.path.exists(ckpt))
+    next_bin = int(np.load(ckpt, allow_pickle=False)["next_bin"]) if have else 0
+    if dist is not None and args.resume:
+        # every rank must resume from the same bin (or none): a missing or older checkpoint on one rank would desynchronise
+        # the sweep counts and deadlock the exchange barriers
+        import torch
+
+        tv = torch.tensor([have, next_bin, -next_bin], dtype=torch.int64, device="cuda")
+        dist.all_reduce(tv, op=dist.ReduceOp.MIN)
+        if int(tv[0]) != have or int(tv[1]) != next_bin or -int(tv[2]) != next_bin:
+            sys.stderr.write(f"ERROR: rank {rank}: checkpoints disagree across ranks (have={have}, next_bin={next_bin}); not resuming\n")
+            raise SystemExit(1)
+    ex_state = None
+    if have:
         z = np.load(ckpt, allow_pickle=False)
+        if "ex_state" in z.files:
+            ex_state = z["ex_state"]
         ctx.set_fields(z["fields"])
         start_bin, therm_done = int(z["next_bin"]), True
         mm.current_bin = start_bin
         mm.datasets = {k[3:]: z[k] for k in z.files if k.startswith("ds:")}
         seed += 7919 * (start_bin + 1)  # fresh stream after a restart
     elif args.rng == "mt19937":
-        base = (int(time.time()) if args.seed is None else args.seed) + rank * args.walkers
+        base = seed0 + rank * args.walkers
         ctx.set_fields(np.stack([host.reference_fields(base + w, nt, N) for w in range(args.walkers)]))
     else:
         model.random_fields(seed)       # GHQField's random start (include/field.h:52-57), one draw per walker
     if args.rng == "mt19937":
-        base = (int(time.time()) if args.seed is None else args.seed) + rank * args.walkers + (7919 * start_bin if therm_done else 0)
+        base = seed0 + rank * args.walkers + (7919 * start_bin if therm_done else 0)
         ctx.rng_seed_mt19937(np.arange(base, base + args.walkers, dtype=np.uint64).astype(np.uint32))
     else:
         ctx.rng_mode(capi.RNG_PHILOX, seed)
@@ -114,6 +150,8 @@ def main(argv=None) -> dict:
 
         eng = parallel.ContextEngine(ctx, local)
         ex = parallel.ReplicaExchange(eng, rank, world, comm_device=torch.device("cuda", local), seed=seed)
+        if ex_state is not None:  # attempt parity and counters continue across a restart
+            ex.attempt, ex.accepted, ex.proposed = (int(x) for x in ex_state)
     if rank == 0:
         save_info(os.path.join(args.out, "info"), L1, L2)
         print(f"{'Parallel Tempering enabled.' if pt else 'Standard DQMC run (Parallel Tempering disabled).'}", flush=True)
@@ -141,11 +179,17 @@ def main(argv=None) -> dict:
         mm.accumulate()
         if args.checkpoint_every and (b + 1) % args.checkpoint_every == 0 and b + 1 < n_bins:
             os.makedirs(args.out, exist_ok=True)
-            np.savez(ckpt, fields=ctx.get_fields(), next_bin=b + 1, **{"ds:" + k: v for k, v in mm.datasets.items()})
+            tmp = ckpt + ".tmp.npz"  # written beside and renamed: a kill during the write never leaves a truncated checkpoint
+            np.savez(tmp, fields=ctx.get_fields(), next_bin=b + 1,
+                     ex_state=np.array([ex.attempt, ex.accepted, ex.proposed] if ex is not None else [0, 0, 0], dtype=np.int64),
+                     **{"ds:" + k: v for k, v in mm.datasets.items()})
+            os.replace(tmp, ckpt)
     ctx.synchronize()
     t_meas = time.perf_counter() - t0
     path = mm.save()
     acc, emax, emean = ctx.get_stats()
+    if unequal:  # the reference folds the unequal-time check_error values into max_err() too (source/dqmc.cpp:264-280)
+        emax = np.maximum(emax, ctx.get_unequal_err())
     n_half = 2.0 * ((n_bins - start_bin) * n_sweeps + (0 if therm_done else n_therms))
     summary = {
         "rank": rank, "beta": beta, "walkers": args.walkers, "bins": n_bins, "file": path,

@@ -138,6 +138,12 @@ void* dqmcb_device_ptr(dqmcb_ctx* ctx, int which);
 /* Observables::calculate_{density,doubleOccupancy,swavePairing,densityCorr} (source/model.cpp:167-288)
  * from the current G: scalars[W][3], corr[W][N*N] (may be NULL). */
 int dqmcb_measure_equal_time(dqmcb_ctx* ctx, double* scalars, double* corr);
+/* Kinetic energy per site and spin correlation from the current G.  NO REFERENCE COUNTERPART (source/model.cpp:167-288 has
+ * neither; BASELINE's north_star names both): by Wick with G_up = G_down = G, ekin[W] = (2t/N) sum_<ij> (G_ij + G_ji) over the
+ * +x / +y bonds of the periodic L1 x L2 lattice, and szz_r[W][L1*L2] (index dx + L1*dy) = (1/N) sum_i <Sz_i Sz_{i+r}> with
+ * <Sz_i Sz_j> = (delta_ij - G_ji) G_ij / 2.  The structure factor is S(q) = sum_r cos(q.r) szz_r.  Parity: pinned on the
+ * analytic U = 0 result and on a numpy restatement (tests/test_gpu_measure.py), not on reference outputs. */
+int dqmcb_measure_kinetic_spin(dqmcb_ctx* ctx, int L1, int L2, double t, double* ekin, double* szz_r);
 /* ---- measurement bins on the device (include/measurementh5.h) ------------------------------------------
  * MeasurementManager::measure (:189-229) / accumulate (:231-274) for the observables source/main.cpp:116-119
  * registers (density, doubleOcc, swave, densityCorr), for all W walkers at once and without leaving the

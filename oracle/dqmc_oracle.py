@@ -511,6 +511,26 @@ def observables(G: np.ndarray):
     return density, docc, swave, corr
 
 
+def kinetic_spin(G: np.ndarray, L1: int, L2: int, t: float = 1.0):
+    """Kinetic energy per site and displacement-folded Sz-Sz correlation from G.  PARITY UNPINNED against the reference:
+    it has no code for either (source/model.cpp:167-288); restated from Wick's theorem with G_up = G_down = G
+    (<c+_i c_j> = delta_ij - G_ji) and pinned on the analytic U = 0 result in tests/test_oracle.py.
+    Returns (ekin, szz_r[dx, dy])."""
+    n = L1 * L2
+    e = 0.0
+    szz = np.zeros((L1, L2))
+    Gc = np.eye(n) - G.T  # <c+_i c_j>
+    for i in range(n):
+        x, y = i % L1, i // L1
+        for j in ((x + 1) % L1 + L1 * y, x + L1 * ((y + 1) % L2)):
+            e += G[j, i] + G[i, j]
+        for dy in range(L2):
+            for dx in range(L1):
+                j = (x + dx) % L1 + L1 * ((y + dy) % L2)
+                szz[dx, dy] += 0.5 * Gc[i, j] * G[i, j]
+    return 2.0 * t * e / n, szz / n
+
+
 # ----------------------------------------------------------------------------------------------
 # Unequal-time observables -- source/model.cpp:290-392 (both spin species share G: factor 2 / square)
 # ----------------------------------------------------------------------------------------------

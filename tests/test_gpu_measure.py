@@ -122,3 +122,33 @@ def test_bin_accumulation_many_walkers_and_reset(tmp_path):
     with pytest.raises(capi.DqmcbError):
         ctx.bin_configure(3, 5)
     ctx.close()
+
+
+@pytest.mark.parametrize("name", ["C1s", "R7", "C0"])
+def test_kinetic_energy_and_spin_correlation_against_restatement(name):
+    """dqmcb_measure_kinetic_spin (no reference counterpart) against oracle.kinetic_spin -- itself pinned on the analytic
+    U = 0 result in tests/test_oracle.py -- on the G of real trajectories: square, ragged 7 x 5 and the 6 x 6 example."""
+    from dqmc_b200 import capi
+    from tests.common import CONFIGS, make_ctx, make_oracle
+
+    cfg = CONFIGS[name]
+    L1, L2, t = cfg[0], cfg[1], cfg[3]
+    W = 3
+    m, _ = make_oracle(cfg, 7)
+    ctx = make_ctx(cfg, W, m.expK, m.invexpK)
+    rng = np.random.default_rng(5)
+    ctx.set_fields(rng.integers(0, 4, size=(W, cfg[6], L1 * L2), dtype=np.int8))
+    ctx.rng_mode(capi.RNG_PHILOX, 11)
+    ctx.init_stacks()
+    ctx.init_greenfunctions()
+    ctx.sweep_0_to_beta()
+    ctx.sweep_beta_to_0()
+    G = ctx.get_G()
+    ekin, szz = ctx.measure_kinetic_spin(L1, L2, t)
+    for w in range(W):
+        e0, s0 = O.kinetic_spin(G[w], L1, L2, t)
+        assert abs(ekin[w] - e0) < 1e-12 * max(1.0, abs(e0))
+        assert np.max(np.abs(szz[w] - s0)) < 1e-12
+    Sq = capi.spin_structure_factor(szz)
+    assert Sq.shape == (W, L1, L2) and np.allclose(Sq[:, 0, 0], szz.sum(axis=(1, 2)))
+    ctx.close()

@@ -322,6 +322,52 @@ def test_kronecker_factor_path_equals_dense_path(monkeypatch):
     assert rel_err(fallback[0], dense[0]) < 1e-7
 
 
+@pytest.mark.parametrize("engine", ["fast", "generic"])
+def test_product_form_matrix_that_is_not_symmetric_takes_the_dense_path(engine, monkeypatch):
+    """The row-wise Kronecker passes feed F(gr, tg) where F(tg, gr) is meant: they need SYMMETRIC factors.  A caller-supplied
+    exp(-dtau K) = Fy (x) Fx with non-symmetric Fx (a valid product form!) must therefore fall back to the dense products:
+    wraps and block products then agree with numpy on the same matrices to 1e-10.  (With the symmetry check missing, the
+    right wrap would silently use Fx^T.)"""
+    from dqmc_b200 import capi, host
+    import math
+
+    if engine == "generic":
+        monkeypatch.setenv("DQMCB_FORCE_GENERIC", "1")
+    else:
+        monkeypatch.delenv("DQMCB_FORCE_GENERIC", raising=False)
+    monkeypatch.delenv("DQMCB_NO_KRON", raising=False)
+    rng = np.random.default_rng(3)
+    Fx = np.eye(8) + 0.1 * rng.standard_normal((8, 8))  # not symmetric
+    Fy = np.eye(8) + 0.05 * rng.standard_normal((8, 8))
+    Fy = 0.5 * (Fy + Fy.T)
+    E = np.kron(Fy, Fx)  # site index x + 8 y
+    Ei = np.linalg.inv(E)
+    nt, n_stab, W, N = 6, 3, 2, 64
+    g = math.sqrt(0.5 * 4.0 * 0.1)
+    ctx = capi.Context(N, nt, n_stab, W, g, host.ETA, host.GAMMA, E, Ei, -1.0, 0, 0)
+    f = rng.integers(0, 4, size=(W, nt, N), dtype=np.int8)
+    ctx.set_fields(f)
+    G0 = np.stack([np.eye(N) * 0.5 + 0.1 * rng.standard_normal((N, N)) for _ in range(W)])
+    ctx.set_G(G0)
+    ctx.wrap_forward(1)
+    Gf = ctx.get_G()
+    ctx.set_G(G0)
+    ctx.wrap_backward(1)
+    Gb = ctx.get_G()
+    B = ctx.block_product(0)
+    eta = np.asarray(host.ETA)
+    for w in range(W):
+        ev = np.exp(g * eta[f[w, 1]])
+        Bl, Bli = ev[:, None] * E, Ei * (1.0 / ev)[None, :]
+        assert rel_err(Gf[w], Bl @ G0[w] @ Bli) < TOL
+        assert rel_err(Gb[w], Bli @ G0[w] @ Bl) < TOL
+        want = np.eye(N)
+        for l in range(n_stab):
+            want = (np.exp(g * eta[f[w, l]])[:, None] * E) @ want
+        assert rel_err(B[w], want) < TOL
+    ctx.close()
+
+
 def test_delayed_updates_with_tiles_in_global_memory_and_shared_sms():
     """Delayed rank-k updates at a size where G no longer fits beside the factors in shared memory
     (N=144, k=32: G lives in the global workspace) and with more walkers than SMs (two CTAs per SM):

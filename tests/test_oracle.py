@@ -428,3 +428,30 @@ def test_restatement_at_full_baseline_configs(name, n_half):
             d.sweep_beta_to_0((tape[0][nt:], tape[1][nt:], tape[2][nt:]))
         assert np.array_equal(m.fields, g["traj_fields"][h]), f"fields diverged from the reference in half sweep {h}"
         assert np.max(np.abs(np.diag(d.G) - g["traj_G_diag"][h])) < 1e-10
+
+
+@pytest.mark.parametrize("L1,L2,mu", [(6, 6, -0.3), (4, 6, 0.2)])
+def test_kinetic_energy_and_spin_structure_factor_known_answer_at_U0(L1, L2, mu):
+    """Kinetic energy and S(q) have no reference code (source/model.cpp:167-288), so the restatement is pinned on the
+    analytic free-fermion result instead: at U = 0 the fields drop out, G = [1 + exp(-beta K)]^-1 exactly, and
+    E_kin / N = (2 / N) sum_k eps_k f(eps_k - mu),   S(q) = (1 / 2N) sum_k f_k (1 - f_{k+q})."""
+    beta, nt, t = 3.0, 30, 1.0
+    n = L1 * L2
+    m = O.Model(L1, L2, 0.0, t, mu, beta, nt, fields=O.random_fields(3, nt, n))
+    d = O.DQMC(m, 10)
+    d.init_stacks()
+    d.init_greenfunctions()
+    ekin, szz = O.kinetic_spin(d.G, L1, L2, t)
+    kx = 2 * np.pi * np.arange(L1) / L1
+    ky = 2 * np.pi * np.arange(L2) / L2
+    eps = -2 * t * (np.cos(kx)[:, None] + np.cos(ky)[None, :])
+    f = 1.0 / (np.exp(beta * (eps - mu)) + 1.0)
+    assert abs(ekin - 2.0 * np.sum(eps * f) / n) < 1e-10
+    Sq = np.real(np.fft.fft2(szz))
+    want = np.empty((L1, L2))
+    for a in range(L1):
+        for b in range(L2):
+            want[a, b] = 0.5 * np.sum(f * (1.0 - np.roll(np.roll(f, -a, axis=0), -b, axis=1))) / n
+    assert np.max(np.abs(Sq - want)) < 1e-10
+    # sum rule: sum_r szz_r = S(q = 0) and szz_r(0) = <Sz^2> = (1/2) <n_up> (1 - <n_up>) per site on average
+    assert abs(szz.sum() - want[0, 0]) < 1e-10

@@ -705,6 +705,14 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
     CKC(cudaFuncSetAttribute(k_uneq_block, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->smem_stab));
     { const char* fg = getenv("DQMCB_FORCE_GENERIC"); ctx->force_generic = fg && fg[0] == (char)49; }
     {
+        // threads per walker of the generic sweep kernels: on small lattices a step of a factorisation has only a few dozen
+        // elements per column, so 256 threads mostly wait at barriers; 64 threads per walker let four to eight walkers share
+        // an SM and interleave their latency chains (C0, N = 36: measured in profiles/r02_generic_threads_c0.json)
+        const char* gt = getenv("DQMCB_GENERIC_THREADS");
+        int t = gt ? atoi(gt) : (N <= 48 ? 64 : kThreads);
+        ctx->gthreads = (t == 32 || t == 64 || t == 128 || t == 256) ? t : kThreads;
+    }
+    {
         const char* pp = getenv("DQMCB_PHASE_PROF");
         if (pp && pp[0] == (char)49) {
             CKC(cudaMalloc(&p.prof, 64 * sizeof(long long)));
@@ -1071,9 +1079,9 @@ static int launch_propagate(dqmcb_ctx* ctx, int l_first, int n_slices, int dir, 
     ctx->n_launches += 1;
     if (fast64_available(ctx)) return fast64_propagate(ctx, p, l_first, n_slices, dir, v0, flags);
     if (p.N >= 128)
-        k_propagate<true><<<p.W, kThreads, ctx->smem_prop, ctx->stream>>>(p, l_first, n_slices, dir, v0, flags);
+        k_propagate<true><<<p.W, ctx->gthreads, ctx->smem_prop, ctx->stream>>>(p, l_first, n_slices, dir, v0, flags);
     else
-        k_propagate<false><<<p.W, kThreads, ctx->smem_prop, ctx->stream>>>(p, l_first, n_slices, dir, v0, flags);
+        k_propagate<false><<<p.W, ctx->gthreads, ctx->smem_prop, ctx->stream>>>(p, l_first, n_slices, dir, v0, flags);
     CK(cudaGetLastError());
     return DQMCB_OK;
 }
@@ -1082,7 +1090,7 @@ int dqmcb_init_stacks(dqmcb_ctx* ctx) {
     NEED(ctx);
     TimeScope ts(ctx, DQMCB_K_INIT);
     ctx->n_launches += 1;
-    if (fast64_available(ctx)) fast_init_stacks(ctx); else k_init_stacks<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p);
+    if (fast64_available(ctx)) fast_init_stacks(ctx); else k_init_stacks<<<ctx->p.W, ctx->gthreads, ctx->smem_stab, ctx->stream>>>(ctx->p);
     CK(cudaGetLastError());
     ctx->stacks_ready = true;
     return DQMCB_OK;
@@ -1095,7 +1103,7 @@ int dqmcb_init_greenfunctions(dqmcb_ctx* ctx) {
     }
     TimeScope ts(ctx, DQMCB_K_INIT);
     ctx->n_launches += 1;
-    if (fast64_available(ctx)) fast_init_green(ctx); else k_init_green<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p);
+    if (fast64_available(ctx)) fast_init_green(ctx); else k_init_green<<<ctx->p.W, ctx->gthreads, ctx->smem_stab, ctx->stream>>>(ctx->p);
     CK(cudaGetLastError());
     ctx->green_ready = true;
     return DQMCB_OK;
@@ -1128,7 +1136,7 @@ int dqmcb_block_product(dqmcb_ctx* ctx, int i_stack) {
         ctx->err = "LDR Stack index out of bounds";
         return DQMCB_EINVAL;
     }
-    if (fast64_available(ctx)) fast_bbar(ctx, i_stack); else k_bbar<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p, i_stack);
+    if (fast64_available(ctx)) fast_bbar(ctx, i_stack); else k_bbar<<<ctx->p.W, ctx->gthreads, ctx->smem_stab, ctx->stream>>>(ctx->p, i_stack);
     CK(cudaGetLastError());
     return DQMCB_OK;
 }
@@ -1141,7 +1149,7 @@ int dqmcb_get_block_product(dqmcb_ctx* ctx, double* out) {
 static int launch_stabilize(dqmcb_ctx* ctx, int l, int dir) {
     TimeScope ts(ctx, DQMCB_K_STABILIZE);
     ctx->n_launches += 1;
-    if (fast64_available(ctx)) fast_stabilize(ctx, l, dir); else k_stabilize<<<ctx->p.W, kThreads, ctx->smem_stab, ctx->stream>>>(ctx->p, l, dir);
+    if (fast64_available(ctx)) fast_stabilize(ctx, l, dir); else k_stabilize<<<ctx->p.W, ctx->gthreads, ctx->smem_stab, ctx->stream>>>(ctx->p, l, dir);
     CK(cudaGetLastError());
     return DQMCB_OK;
 }

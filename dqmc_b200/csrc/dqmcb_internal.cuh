@@ -118,6 +118,7 @@ struct dqmcb_ctx {
     cudaEvent_t gdone[8] = {};
     cudaEvent_t ev_fork = nullptr;
     long long n_launches = 0;  // kernels launched by this context so far (dqmcb_launch_count)
+    int gthreads = dq::kThreads;  // threads per CTA of the generic sweep kernels (64 on small lattices)
     bool use_stab2 = false;      // N = 64 with Kronecker factors: second-generation stabilisation kernel (stab2.cuh)
     bool force_generic = false;  // DQMCB_FORCE_GENERIC=1: bypass the compile-time-N fast path (parity cross-checks)
     bool timing = false;

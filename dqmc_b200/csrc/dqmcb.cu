@@ -137,11 +137,11 @@ __global__ void __launch_bounds__(kThreads) k_stabilize(Params p, int l, int dir
             // mat_mul_ldr (source/stablelinalg.cpp:69-79): (Bbar L) D -> QR ; R <- R_new R_old
             store_d(wk.sv[0], stkD(p, w, i - 1), n);
             __syncthreads();
-            cta_gemm<false>(b1, l1, b0, 1, l0, stkL(p, w, i - 1), 1, n, n, nullptr, wk.sv[0]);
+            dev_gemm<false>(wk, b1, l1, b0, 1, l0, stkL(p, w, i - 1), 1, n, n, nullptr, wk.sv[0]);
             DQ_PH(p, 2);
             dev_to_ldr(wk, n, b1, l1, b0, l0, b2, l2, wk.dnew);
             DQ_PH(p, 3);
-            cta_gemm<false>(stkR(p, w, i), n, b2, 1, l2, stkR(p, w, i - 1), 1, n, n, nullptr, nullptr);
+            dev_gemm<false>(wk, stkR(p, w, i), n, b2, 1, l2, stkR(p, w, i - 1), 1, n, n, nullptr, nullptr);
             cta_copy(stkL(p, w, i), n, b0, l0, n);
         }
     } else {
@@ -154,9 +154,9 @@ __global__ void __launch_bounds__(kThreads) k_stabilize(Params p, int l, int dir
             // ldr_mul_mat (source/stablelinalg.cpp:57-67): D (R Bbar) -> QR ; L <- L_old Q
             store_d(wk.sv[0], stkD(p, w, i + 1), n);
             __syncthreads();
-            cta_gemm<false>(b1, l1, stkR(p, w, i + 1), 1, n, b0, 1, l0, n, wk.sv[0], nullptr);
+            dev_gemm<false>(wk, b1, l1, stkR(p, w, i + 1), 1, n, b0, 1, l0, n, wk.sv[0], nullptr);
             dev_to_ldr(wk, n, b1, l1, b0, l0, b2, l2, wk.dnew);
-            cta_gemm<false>(stkL(p, w, i), n, stkL(p, w, i + 1), 1, n, b0, 1, l0, n, nullptr, nullptr);
+            dev_gemm<false>(wk, stkL(p, w, i), n, stkL(p, w, i + 1), 1, n, b0, 1, l0, n, nullptr, nullptr);
             cta_copy(stkR(p, w, i), n, b2, l2, n);
         }
     }
@@ -223,16 +223,16 @@ __global__ void __launch_bounds__(kThreads) k_init_stacks(Params p) {
             store_d(wk.sv[0], stkD(p, w, i + 1), n);
             __syncthreads();
             // M' = D1 (R1 L2) D2 -> b0
-            cta_gemm<false>(b0, l0, stkR(p, w, i + 1), 1, n, b1, 1, l1, n, wk.sv[0], wk.sv[2]);
+            dev_gemm<false>(wk, b0, l0, stkR(p, w, i + 1), 1, n, b1, 1, l1, n, wk.sv[0], wk.sv[2]);
             // keep R2 (b2) : factor b0 -> Q in b1 (L2 no longer needed), Rn in global R slot as temp
             double* Rtmp = stkR(p, w, i);
             dev_to_ldr(wk, n, b0, l0, b1, l1, Rtmp, n, wk.dnew);
             // L = L1 Q
-            cta_gemm<false>(stkL(p, w, i), n, stkL(p, w, i + 1), 1, n, b1, 1, l1, n, nullptr, nullptr);
+            dev_gemm<false>(wk, stkL(p, w, i), n, stkL(p, w, i + 1), 1, n, b1, 1, l1, n, nullptr, nullptr);
             // R = R_new R2  (Rtmp -> b0 first, then product into the global slot)
             cta_copy(b0, l0, Rtmp, n, n);
             __syncthreads();
-            cta_gemm<false>(Rtmp, n, b0, 1, l0, b2, 1, l2, n, nullptr, nullptr);
+            dev_gemm<false>(wk, Rtmp, n, b0, 1, l0, b2, 1, l2, n, nullptr, nullptr);
             store_d(stkD(p, w, i), wk.dnew, n);
         }
         __syncthreads();
@@ -343,27 +343,27 @@ __global__ void __launch_bounds__(kThreads) k_ldr_op(Params p, int op, LdrArgs a
     } else if (op == 1) {  // mat_mul_ldr(M, F1)
         store_d(wk.sv[0], d1, n);
         __syncthreads();
-        cta_gemm<false>(b1, l1, M, 1, n, L1, 1, n, n, nullptr, wk.sv[0]);
+        dev_gemm<false>(wk, b1, l1, M, 1, n, L1, 1, n, n, nullptr, wk.sv[0]);
         dev_to_ldr(wk, n, b1, l1, b0, l0, b2, l2, wk.dnew);
-        cta_gemm<false>(Ro, n, b2, 1, l2, R1, 1, n, n, nullptr, nullptr);
+        dev_gemm<false>(wk, Ro, n, b2, 1, l2, R1, 1, n, n, nullptr, nullptr);
         cta_copy(Lo, n, b0, l0, n);
         store_d(dO, wk.dnew, n);
     } else if (op == 2) {  // ldr_mul_mat(F1, M)
         store_d(wk.sv[0], d1, n);
         __syncthreads();
-        cta_gemm<false>(b1, l1, R1, 1, n, M, 1, n, n, wk.sv[0], nullptr);
+        dev_gemm<false>(wk, b1, l1, R1, 1, n, M, 1, n, n, wk.sv[0], nullptr);
         dev_to_ldr(wk, n, b1, l1, b0, l0, b2, l2, wk.dnew);
-        cta_gemm<false>(Lo, n, L1, 1, n, b0, 1, l0, n, nullptr, nullptr);
+        dev_gemm<false>(wk, Lo, n, L1, 1, n, b0, 1, l0, n, nullptr, nullptr);
         cta_copy(Ro, n, b2, l2, n);
         store_d(dO, wk.dnew, n);
     } else if (op == 3) {  // ldr_mul_ldr(F1, F2)
         store_d(wk.sv[0], d1, n);
         store_d(wk.sv[2], d2, n);
         __syncthreads();
-        cta_gemm<false>(b0, l0, R1, 1, n, L2, 1, n, n, wk.sv[0], wk.sv[2]);
+        dev_gemm<false>(wk, b0, l0, R1, 1, n, L2, 1, n, n, wk.sv[0], wk.sv[2]);
         dev_to_ldr(wk, n, b0, l0, b1, l1, b2, l2, wk.dnew);
-        cta_gemm<false>(Lo, n, L1, 1, n, b1, 1, l1, n, nullptr, nullptr);
-        cta_gemm<false>(Ro, n, b2, 1, l2, R2, 1, n, n, nullptr, nullptr);
+        dev_gemm<false>(wk, Lo, n, L1, 1, n, b1, 1, l1, n, nullptr, nullptr);
+        dev_gemm<false>(wk, Ro, n, b2, 1, l2, R2, 1, n, n, nullptr, nullptr);
         store_d(dO, wk.dnew, n);
     } else if (op == 4) {
         const double ld_ = dev_inv_I_plus_ldr(p, wk, n, L1, n, d1, R1, n);
@@ -532,6 +532,17 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
     const int N = cfg->n_sites, W = cfg->n_walkers, nt = cfg->nt;
     p.N = N;
     p.LD = (N % 2 == 0) ? N + 1 : N;  // odd leading dimension: conflict-free row access in SMEM
+    {
+        // N = 256: no tile of the walker fits in shared memory, so the work tiles stay in global memory with a DENSE leading
+        // dimension (16-byte-aligned columns for cp.async.bulk) and shared memory holds the operand panels of gemm_tma.cuh
+        const size_t sb0 = ((small_bytes(N) + 15) & ~(size_t)15);
+        const char* nt_ = getenv("DQMCB_NO_TMA_GEMM");
+        if (N == kGT_N && sb0 + (size_t)N * p.LD * 8 > (size_t)kMaxSmem && sb0 + kGemmTmaArenaBytes <= (size_t)kMaxSmem &&
+            !(nt_ && nt_[0] == (char)49)) {
+            p.LD = N;
+            p.smem_arena = 1;
+        }
+    }
     p.nt = nt;
     p.n_stab = cfg->n_stab;
     p.n_stack = (nt + cfg->n_stab - 1) / cfg->n_stab;
@@ -684,7 +695,7 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
     const size_t sb = ((small_bytes(N) + 15) & ~(size_t)15);
     p.smem_mats_stab = (sb + 3 * tile <= (size_t)kMaxSmem) ? 3 : 0;
     p.smem_stage = (p.smem_mats_stab == 0 && sb + tile <= (size_t)kMaxSmem) ? 1 : 0;
-    ctx->smem_stab = sb + (p.smem_mats_stab + p.smem_stage) * tile;
+    ctx->smem_stab = sb + (p.smem_mats_stab + p.smem_stage) * tile + (p.smem_arena ? kGemmTmaArenaBytes : 0);
     p.delay_k = (cfg->delay_k > 1) ? std::min(cfg->delay_k, 64) : 0;
     const size_t pb = prop_small_bytes(N);
     const size_t dly = p.delay_k ? ((size_t)2 * p.delay_k * N + 2 * N) * 8 : 0;

@@ -8,6 +8,7 @@
 #pragma once
 #include "dqmcb_internal.cuh"
 #include "linalg.cuh"
+#include "gemm_tma.cuh"
 
 namespace dq {
 
@@ -21,6 +22,7 @@ struct Work {
     int lds;
     double *tau, *vn1, *vn2, *sv[4], *dnew, *prow, *jrow, *red;
     int *jpvt, *ipiv, *info;
+    unsigned char* arena;  // operand panels of cta_gemm_tma256 (N = 256), else null
 };
 
 __host__ __device__ inline size_t small_bytes(int N) {
@@ -48,6 +50,7 @@ __device__ inline void carve(Work& wk, const Params& p, int walker, int nmats_sm
     double* tiles = reinterpret_cast<double*>(smem + ((small_bytes(N) + 15) & ~(size_t)15));
     wk.stage = (nmats_smem == 0 && p.smem_stage) ? tiles : nullptr;
     wk.lds = p.LD;
+    wk.arena = (nmats_smem == 0 && !p.smem_stage && p.smem_arena) ? reinterpret_cast<unsigned char*>(tiles) : nullptr;
     double* gws = p.ws + (size_t)walker * 3 * N * p.LD;
     for (int i = 0; i < 3; ++i) {
         if (i < nmats_smem) {
@@ -58,6 +61,18 @@ __device__ inline void carve(Work& wk, const Params& p, int walker, int nmats_sm
             wk.ld[i] = p.LD;
         }
     }
+}
+
+// Product of the stabilisation kernels: the TMA-staged kernel when the walker has its shared-memory arena (N = 256, both
+// operands column-major with 16-byte-aligned columns), else the register-ring / FMA product of linalg.cuh.
+template <bool ACC>
+__device__ __forceinline__ void dev_gemm(const Work& wk, double* C, int ldc, const double* A, int rsA, int csA, const double* B, int rsB,
+                                         int csB, int n, const double* rs, const double* cs) {
+    if (wk.arena && n == kGT_N && blockDim.x == 256 && rsA == 1 && rsB == 1 && !(csA & 1) && !(csB & 1) &&
+        !((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15))
+        cta_gemm_tma256(C, ldc, A, csA, B, csB, rs, cs, ACC, wk.arena);
+    else
+        cta_gemm<ACC>(C, ldc, A, rsA, csA, B, rsB, csB, n, rs, cs);
 }
 
 __device__ inline double cta_reduce_sum(double v, double* red) {
@@ -222,12 +237,22 @@ __device__ void dev_inv_I_plus_ldr_mul_ldr(const Params& p, Work& wk, int n, con
     __syncthreads();
     DQ_PH(p, 7);
     // TermA = D1l^-1 (L1^T X)
-    cta_gemm<false>(b2, l2, L1, ldg, 1, b1, 1, l1, n, wk.sv[0], nullptr);
+    if (wk.arena) {  // L1^T materialised in b0 (free between the two factorisations): both operands column-major for the staged product
+        for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
+            const int r = e % n, c = e / n;
+            b0[r + (size_t)c * l0] = L1[c + (size_t)r * ldg];
+        }
+        __syncthreads();
+        dev_gemm<false>(wk, b2, l2, b0, 1, l0, b1, 1, l1, n, wk.sv[0], nullptr);
+        __syncthreads();
+    } else {
+        cta_gemm<false>(b2, l2, L1, ldg, 1, b1, 1, l1, n, wk.sv[0], nullptr);
+    }
     // b0 = L2 D2s
     cta_copy(b0, l0, L2, ldg, n, nullptr, wk.sv[3]);
     __syncthreads();
     // M = TermA + D1s (R1 (L2 D2s))
-    cta_gemm<true>(b2, l2, R1, 1, ldg, b0, 1, l0, n, wk.sv[1], nullptr);
+    dev_gemm<true>(wk, b2, l2, R1, 1, ldg, b0, 1, l0, n, wk.sv[1], nullptr);
     __syncthreads();
     double* f2 = b2;
     int lf2 = l2;
@@ -249,7 +274,7 @@ __device__ void dev_inv_I_plus_ldr_mul_ldr(const Params& p, Work& wk, int n, con
     cta_lu_solve(f2, lf2, n, wk.ipiv, b0, 1, l0, true);  // Y = M^-1 RHS
     __syncthreads();
     DQ_PH(p, 11);
-    cta_gemm<false>(b2, l2, b1, 1, l1, b0, 1, l0, n, nullptr, nullptr);  // G = X Y
+    dev_gemm<false>(wk, b2, l2, b1, 1, l1, b0, 1, l0, n, nullptr, nullptr);  // G = X Y
     __syncthreads();
 }
 

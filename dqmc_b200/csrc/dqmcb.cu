@@ -115,52 +115,64 @@ __device__ inline void store_d(double* dst, const double* src, int n) {
 
 // End-of-block work of the sweeps (source/dqmc.cpp:369-394 forward, 429-454 backward):
 // Bbar from the current fields, stack update, stabilised G, check_error against the wrapped G.
-__global__ void __launch_bounds__(kThreads) k_stabilize(Params p, int l, int dir) {
+// `part`: 0 = everything in one launch.  N = 256 runs it as three launches (1: block product and the product with the
+// neighbouring stack factor, 2: the pivoted QR, 3: the rest) because the two halves want opposite shared-memory carve-outs:
+// the TMA-staged products and solves need ~200 KB of operand panels, while the QR -- whose trailing matrix fits in L1
+// for its last ~150 steps -- loses 30% when that shared memory leaves it no L1.  All state that crosses a part boundary
+// lives in the walker's global work tiles (b0..b2) and in the stack entry itself.
+__global__ void __launch_bounds__(kThreads) k_stabilize(Params p, int l, int dir, int part) {
     extern __shared__ __align__(16) unsigned char smem[];
     const int w = blockIdx.x, n = p.N;
     Work wk;
     carve(wk, p, w, p.smem_mats_stab, smem);
     const int i = l / p.n_stab;
-    DQ_PH(p, 0);
-    dev_bbar(p, wk, w, i);  // -> b[0]
-    DQ_PH(p, 1);
+    const bool do1 = part == 0 || part == 1, do2 = part == 0 || part == 2, do3 = part == 0 || part == 3;
     double *b0 = wk.b[0], *b1 = wk.b[1], *b2 = wk.b[2];
     const int l0 = wk.ld[0], l1 = wk.ld[1], l2 = wk.ld[2];
-    __syncthreads();
-    if (dir > 0) {
-        // update_stack_forward (source/dqmc.cpp:134-146)
-        if (i == 0) {
-            dev_to_ldr(wk, n, b0, l0, b1, l1, b2, l2, wk.dnew);
-            cta_copy(stkL(p, w, i), n, b1, l1, n);
-            cta_copy(stkR(p, w, i), n, b2, l2, n);
-        } else {
-            // mat_mul_ldr (source/stablelinalg.cpp:69-79): (Bbar L) D -> QR ; R <- R_new R_old
-            store_d(wk.sv[0], stkD(p, w, i - 1), n);
+    const bool first = (dir > 0) ? (i == 0) : (i == p.n_stack - 1);  // the stack entry is to_LDR(Bbar) itself
+    if (do1) {
+        DQ_PH(p, 0);
+        dev_bbar(p, wk, w, i);  // -> b[0]
+        DQ_PH(p, 1);
+        __syncthreads();
+        if (!first) {
+            if (dir > 0) {
+                // update_stack_forward (source/dqmc.cpp:134-146): mat_mul_ldr (source/stablelinalg.cpp:69-79): (Bbar L) D -> QR
+                store_d(wk.sv[0], stkD(p, w, i - 1), n);
+                __syncthreads();
+                dev_gemm<false>(wk, b1, l1, b0, 1, l0, stkL(p, w, i - 1), 1, n, n, nullptr, wk.sv[0]);
+            } else {
+                // update_stack_backward (source/dqmc.cpp:189-201): ldr_mul_mat (source/stablelinalg.cpp:57-67): D (R Bbar) -> QR
+                store_d(wk.sv[0], stkD(p, w, i + 1), n);
+                __syncthreads();
+                dev_gemm<false>(wk, b1, l1, stkR(p, w, i + 1), 1, n, b0, 1, l0, n, wk.sv[0], nullptr);
+            }
             __syncthreads();
-            dev_gemm<false>(wk, b1, l1, b0, 1, l0, stkL(p, w, i - 1), 1, n, n, nullptr, wk.sv[0]);
-            DQ_PH(p, 2);
-            dev_to_ldr(wk, n, b1, l1, b0, l0, b2, l2, wk.dnew);
-            DQ_PH(p, 3);
-            dev_gemm<false>(wk, stkR(p, w, i), n, b2, 1, l2, stkR(p, w, i - 1), 1, n, n, nullptr, nullptr);
-            cta_copy(stkL(p, w, i), n, b0, l0, n);
         }
-    } else {
-        // update_stack_backward (source/dqmc.cpp:189-201)
-        if (i == p.n_stack - 1) {
-            dev_to_ldr(wk, n, b0, l0, b1, l1, b2, l2, wk.dnew);
-            cta_copy(stkL(p, w, i), n, b1, l1, n);
-            cta_copy(stkR(p, w, i), n, b2, l2, n);
-        } else {
-            // ldr_mul_mat (source/stablelinalg.cpp:57-67): D (R Bbar) -> QR ; L <- L_old Q
-            store_d(wk.sv[0], stkD(p, w, i + 1), n);
-            __syncthreads();
-            dev_gemm<false>(wk, b1, l1, stkR(p, w, i + 1), 1, n, b0, 1, l0, n, wk.sv[0], nullptr);
-            dev_to_ldr(wk, n, b1, l1, b0, l0, b2, l2, wk.dnew);
-            dev_gemm<false>(wk, stkL(p, w, i), n, stkL(p, w, i + 1), 1, n, b0, 1, l0, n, nullptr, nullptr);
-            cta_copy(stkR(p, w, i), n, b2, l2, n);
-        }
+        DQ_PH(p, 2);
     }
-    store_d(stkD(p, w, i), wk.dnew, n);
+    if (do2) {
+        if (first)
+            dev_to_ldr(wk, n, b0, l0, b1, l1, b2, l2, wk.dnew);
+        else
+            dev_to_ldr(wk, n, b1, l1, b0, l0, b2, l2, wk.dnew);
+        store_d(stkD(p, w, i), wk.dnew, n);
+        __syncthreads();
+        DQ_PH(p, 3);
+    }
+    if (!do3) return;
+    if (first) {
+        cta_copy(stkL(p, w, i), n, b1, l1, n);
+        cta_copy(stkR(p, w, i), n, b2, l2, n);
+    } else if (dir > 0) {
+        // R <- R_new R_old
+        dev_gemm<false>(wk, stkR(p, w, i), n, b2, 1, l2, stkR(p, w, i - 1), 1, n, n, nullptr, nullptr);
+        cta_copy(stkL(p, w, i), n, b0, l0, n);
+    } else {
+        // L <- L_old Q
+        dev_gemm<false>(wk, stkL(p, w, i), n, stkL(p, w, i + 1), 1, n, b0, 1, l0, n, nullptr, nullptr);
+        cta_copy(stkR(p, w, i), n, b2, l2, n);
+    }
     __syncthreads();  // stack entry i visible to the whole CTA (global writes + barrier)
     DQ_PH(p, 4);
     // stabilize_GF_* (source/dqmc.cpp:148-161, 203-215)
@@ -417,6 +429,27 @@ static thread_local std::string g_create_err;
         }                                                                                         \
     } while (0)
 
+// Shared-memory plan of the stabilisation kernels for an n-site walker: leading dimension of the work tiles and which of
+// {three resident tiles, one staging tile, the TMA operand arena of gemm_tma.cuh} shared memory holds.  Returns the bytes.
+static size_t plan_stab_smem(Params& p, int n) {
+    p.LD = (n % 2 == 0) ? n + 1 : n;  // odd leading dimension: conflict-free row access in SMEM
+    p.smem_arena = 0;
+    const size_t sb = ((small_bytes(n) + 15) & ~(size_t)15);
+    const char* nt_ = getenv("DQMCB_NO_TMA_GEMM");
+    // N = 256: no tile of the walker fits in shared memory, so the work tiles stay in global memory with an EVEN leading
+    // dimension (16-byte-aligned columns for cp.async.bulk; n + 2 rather than n: with columns exactly 2 KB apart the
+    // column-wise factorisations pile onto a few L2 slices, measured +30% on the QR) and shared memory holds the operand
+    // panels of gemm_tma.cuh
+    if (n == kGT_N && sb + (size_t)n * p.LD * 8 > (size_t)kMaxSmem && sb + kGemmTmaArenaBytes <= (size_t)kMaxSmem && !(nt_ && nt_[0] == (char)49)) {
+        p.LD = n + 2;
+        p.smem_arena = 1;
+    }
+    const size_t tile = (size_t)n * p.LD * 8;
+    p.smem_mats_stab = (sb + 3 * tile <= (size_t)kMaxSmem) ? 3 : 0;
+    p.smem_stage = (!p.smem_arena && p.smem_mats_stab == 0 && sb + tile <= (size_t)kMaxSmem) ? 1 : 0;
+    return sb + (p.smem_mats_stab + p.smem_stage) * tile + (p.smem_arena ? kGemmTmaArenaBytes : 0);
+}
+
 static size_t prop_small_bytes(int n) {
     size_t off = (size_t)(5 * n) * 8 + (size_t)(3 * n) * 4 + (size_t)n;
     return (off + 15) & ~(size_t)15;
@@ -531,18 +564,7 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
     memset(&p, 0, sizeof(p));
     const int N = cfg->n_sites, W = cfg->n_walkers, nt = cfg->nt;
     p.N = N;
-    p.LD = (N % 2 == 0) ? N + 1 : N;  // odd leading dimension: conflict-free row access in SMEM
-    {
-        // N = 256: no tile of the walker fits in shared memory, so the work tiles stay in global memory with a DENSE leading
-        // dimension (16-byte-aligned columns for cp.async.bulk) and shared memory holds the operand panels of gemm_tma.cuh
-        const size_t sb0 = ((small_bytes(N) + 15) & ~(size_t)15);
-        const char* nt_ = getenv("DQMCB_NO_TMA_GEMM");
-        if (N == kGT_N && sb0 + (size_t)N * p.LD * 8 > (size_t)kMaxSmem && sb0 + kGemmTmaArenaBytes <= (size_t)kMaxSmem &&
-            !(nt_ && nt_[0] == (char)49)) {
-            p.LD = N;
-            p.smem_arena = 1;
-        }
-    }
+    const size_t stab_smem = plan_stab_smem(p, N);
     p.nt = nt;
     p.n_stab = cfg->n_stab;
     p.n_stack = (nt + cfg->n_stab - 1) / cfg->n_stab;
@@ -693,9 +715,7 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
     // shared-memory plan
     const size_t tile = (size_t)N * p.LD * 8;
     const size_t sb = ((small_bytes(N) + 15) & ~(size_t)15);
-    p.smem_mats_stab = (sb + 3 * tile <= (size_t)kMaxSmem) ? 3 : 0;
-    p.smem_stage = (p.smem_mats_stab == 0 && sb + tile <= (size_t)kMaxSmem) ? 1 : 0;
-    ctx->smem_stab = sb + (p.smem_mats_stab + p.smem_stage) * tile + (p.smem_arena ? kGemmTmaArenaBytes : 0);
+    ctx->smem_stab = stab_smem;
     p.delay_k = (cfg->delay_k > 1) ? std::min(cfg->delay_k, 64) : 0;
     const size_t pb = prop_small_bytes(N);
     const size_t dly = p.delay_k ? ((size_t)2 * p.delay_k * N + 2 * N) * 8 : 0;
@@ -1160,7 +1180,20 @@ int dqmcb_get_block_product(dqmcb_ctx* ctx, double* out) {
 static int launch_stabilize(dqmcb_ctx* ctx, int l, int dir) {
     TimeScope ts(ctx, DQMCB_K_STABILIZE);
     ctx->n_launches += 1;
-    if (fast64_available(ctx)) fast_stabilize(ctx, l, dir); else k_stabilize<<<ctx->p.W, ctx->gthreads, ctx->smem_stab, ctx->stream>>>(ctx->p, l, dir);
+    if (fast64_available(ctx)) {
+        fast_stabilize(ctx, l, dir);
+    } else if (ctx->p.smem_arena) {
+        // N = 256: three launches (see k_stabilize); the middle one without the operand arena, i.e. with a large L1
+        Params p2 = ctx->p;
+        p2.smem_arena = 0;
+        const size_t sb = ctx->smem_stab - kGemmTmaArenaBytes;
+        k_stabilize<<<ctx->p.W, ctx->gthreads, ctx->smem_stab, ctx->stream>>>(ctx->p, l, dir, 1);
+        k_stabilize<<<ctx->p.W, ctx->gthreads, sb, ctx->stream>>>(p2, l, dir, 2);
+        k_stabilize<<<ctx->p.W, ctx->gthreads, ctx->smem_stab, ctx->stream>>>(ctx->p, l, dir, 3);
+        ctx->n_launches += 2;
+    } else {
+        k_stabilize<<<ctx->p.W, ctx->gthreads, ctx->smem_stab, ctx->stream>>>(ctx->p, l, dir, 0);
+    }
     CK(cudaGetLastError());
     return DQMCB_OK;
 }
@@ -1688,13 +1721,9 @@ static int run_ldr_op(int device, int n, int batch, int op, const double* M, con
     Params p;
     memset(&p, 0, sizeof(p));
     p.N = n;
-    p.LD = (n % 2 == 0) ? n + 1 : n;
+    const size_t smem = plan_stab_smem(p, n);
     p.W = batch;
     const size_t nn = (size_t)n * n, tile = (size_t)n * p.LD * 8;
-    const size_t sb = ((small_bytes(n) + 15) & ~(size_t)15);
-    p.smem_mats_stab = (sb + 3 * tile <= (size_t)kMaxSmem) ? 3 : 0;
-    p.smem_stage = (p.smem_mats_stab == 0 && sb + tile <= (size_t)kMaxSmem) ? 1 : 0;
-    const size_t smem = sb + (p.smem_mats_stab + p.smem_stage) * tile;
     std::vector<void*> allocs;
     int rc = DQMCB_OK;
     auto up = [&](const double* h, size_t cnt) -> double* {

@@ -75,6 +75,15 @@ __device__ __forceinline__ void dev_gemm(const Work& wk, double* C, int ldc, con
         cta_gemm<ACC>(C, ldc, A, rsA, csA, B, rsB, csB, n, rs, cs);
 }
 
+// Solve with a cta_lu factorisation on a right-hand side written with its rows already interchanged.
+__device__ __forceinline__ void dev_lu_solve_prepermuted(const Work& wk, const double* A, int lda, int n, double* Bm, int ldb) {
+    if (wk.arena && n == kGT_N && blockDim.x == 256 && !(lda & 1) && !(ldb & 1) &&
+        !((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(Bm)) & 15))
+        cta_lu_solve_tma256(A, lda, Bm, ldb, wk.arena);
+    else
+        cta_lu_solve(A, lda, n, wk.ipiv, Bm, 1, ldb, true);
+}
+
 __device__ inline double cta_reduce_sum(double v, double* red) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     v = warp_sum(v);
@@ -233,16 +242,12 @@ __device__ void dev_inv_I_plus_ldr_mul_ldr(const Params& p, Work& wk, int n, con
         b1[r + (size_t)c * l1] = (wk.jpvt[r] == c) ? wk.sv[2][c] : 0.0;
     }
     __syncthreads();
-    cta_lu_solve(f0, lf0, n, wk.ipiv, b1, 1, l1, true);  // X = R2^-1 D2_large^-1
+    dev_lu_solve_prepermuted(wk, f0, lf0, n, b1, l1);  // X = R2^-1 D2_large^-1
     __syncthreads();
     DQ_PH(p, 7);
     // TermA = D1l^-1 (L1^T X)
-    if (wk.arena) {  // L1^T materialised in b0 (free between the two factorisations): both operands column-major for the staged product
-        for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
-            const int r = e % n, c = e / n;
-            b0[r + (size_t)c * l0] = L1[c + (size_t)r * ldg];
-        }
-        __syncthreads();
+    if (wk.arena && n == kGT_N && blockDim.x == 256) {  // L1^T materialised in b0 (free between the two factorisations): both operands column-major for the staged product
+        cta_transpose256(b0, l0, L1, ldg, wk.arena);
         dev_gemm<false>(wk, b2, l2, b0, 1, l0, b1, 1, l1, n, wk.sv[0], nullptr);
         __syncthreads();
     } else {
@@ -271,7 +276,7 @@ __device__ void dev_inv_I_plus_ldr_mul_ldr(const Params& p, Work& wk, int n, con
         b0[r + (size_t)c * l0] = rhs_mode ? wk.sv[1][pr] * R1[pr + (size_t)c * ldg] : wk.sv[0][pr] * L1[c + (size_t)pr * ldg];
     }
     __syncthreads();
-    cta_lu_solve(f2, lf2, n, wk.ipiv, b0, 1, l0, true);  // Y = M^-1 RHS
+    dev_lu_solve_prepermuted(wk, f2, lf2, n, b0, l0);  // Y = M^-1 RHS
     __syncthreads();
     DQ_PH(p, 11);
     dev_gemm<false>(wk, b2, l2, b1, 1, l1, b0, 1, l0, n, nullptr, nullptr);  // G = X Y

@@ -149,7 +149,7 @@ def test_trajectory(name, n_sweeps, delay_k):
         assert rel_err(corr[w], cc) < 1e-9
 
 
-@pytest.mark.parametrize("n", [36, 64, 35])
+@pytest.mark.parametrize("n", [36, 64, 35, 144, 256])  # 144: staging tile; 256: TMA-staged products and solves (gemm_tma.cuh)
 def test_stablelinalg_batched(n):
     """source/stablelinalg.cpp functions one by one on graded random matrices."""
     from dqmc_b200 import capi

@@ -198,11 +198,23 @@ __global__ void __launch_bounds__(kThreads) k_stabilize(Params p, int l, int dir
     // check_error (source/dqmc.cpp:317-329) + install the stabilised G
     double* Gg = p.G + (size_t)w * n * n;
     double emax = 0.0;
-    for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
-        const int r = e % n, c = e / n;
-        const double v = Gnew[r + (size_t)c * ldn];
-        emax = fmax(emax, fabs(Gg[e] - v));
-        Gg[e] = v;
+    for (int e0 = threadIdx.x; e0 < n * n; e0 += 4 * blockDim.x) {  // 8 loads in flight per thread
+        double v[4], g[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int e = e0 + u * blockDim.x;
+            const bool ok = e < n * n;
+            v[u] = ok ? Gnew[e % n + (size_t)(e / n) * ldn] : 0.0;
+            g[u] = ok ? Gg[e] : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int e = e0 + u * blockDim.x;
+            if (e < n * n) {
+                emax = fmax(emax, fabs(g[u] - v[u]));
+                Gg[e] = v[u];
+            }
+        }
     }
     emax = cta_reduce_max(emax, wk.red);
     DQ_PH(p, 13);

@@ -270,10 +270,20 @@ __device__ void dev_inv_I_plus_ldr_mul_ldr(const Params& p, Work& wk, int n, con
     //                                  source/stablelinalg.cpp:160-190 -- same M, different right-hand side),
     // built after the factorisation so that it can be written with its rows already interchanged
     cta_perm_from_ipiv(wk.ipiv, wk.jpvt, n);
-    for (int e = threadIdx.x; e < n * n; e += blockDim.x) {
-        const int r = e % n, c = e / n;
-        const int pr = wk.jpvt[r];
-        b0[r + (size_t)c * l0] = rhs_mode ? wk.sv[1][pr] * R1[pr + (size_t)c * ldg] : wk.sv[0][pr] * L1[c + (size_t)pr * ldg];
+    for (int e0 = threadIdx.x; e0 < n * n; e0 += 4 * blockDim.x) {  // four loads in flight per thread
+        double v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int e = e0 + u * blockDim.x;
+            const int r = e % n, c = e / n;
+            const int pr = wk.jpvt[r];
+            v[u] = (e < n * n) ? (rhs_mode ? wk.sv[1][pr] * R1[pr + (size_t)c * ldg] : wk.sv[0][pr] * L1[c + (size_t)pr * ldg]) : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const int e = e0 + u * blockDim.x;
+            if (e < n * n) b0[e % n + (size_t)(e / n) * l0] = v[u];
+        }
     }
     __syncthreads();
     dev_lu_solve_prepermuted(wk, f2, lf2, n, b0, l0);  // Y = M^-1 RHS
@@ -296,8 +306,32 @@ __device__ void dev_bbar(const Params& p, Work& wk, int walker, int i_stack) {
     if (p.kg) {
         // Kronecker chain in place in b[0]: B_l X = diag(ev_l) (Fy (x) Fx) X; a warp keeps its column groups for the whole
         // chain, so the slices need no barrier for the matrix itself
-        double* X = wk.b[0];
-        const int ldx = wk.ld[0];
+        if (wk.arena && n == kGT_N && p.kL1 == 16 && p.kL2 == 16 && blockDim.x == 256 && l1 - l0 <= 2 * kGT_KP * kGT_LDS / kGT_N) {
+            // N = 256: the chain acts on every column separately, so each warp takes 8 columns of a 64-column panel in shared
+            // memory through ALL slices of the block (no block barrier, no L2 round trip per slice) and writes them out once
+            double* panel = reinterpret_cast<double*>(wk.arena + 64);
+            double* sc = panel + (size_t)kGT_LDS * kGT_CP;  // exp(g eta) of every slice of the block
+            const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+            __syncthreads();
+            for (int e = threadIdx.x; e < (l1 - l0) * n; e += blockDim.x) sc[e] = p.lut_ev[f[(size_t)l0 * n + e]];
+            __syncthreads();
+            double* mine = panel + (size_t)(8 * warp) * kGT_LDS;
+            for (int c0 = 8 * warp; c0 < n; c0 += kGT_CP) {
+                for (int q = 0; q < 8; ++q)  // B_{l0} = diag(ev) expK, this warp's columns
+                    for (int r = lane; r < n; r += 32) mine[r + (size_t)q * kGT_LDS] = sc[r] * p.expK[r + (size_t)(c0 + q) * n];
+                __syncwarp();
+                for (int l = 1; l < l1 - l0; ++l)
+                    cta_kron_apply_ct<16, 16, false, 4>(panel, kGT_LDS, p.kg, p.kg + 256, nullptr, sc + (size_t)l * n, warp);
+                for (int q = 0; q < 8; ++q)
+                    for (int r = lane; r < n; r += 32) wk.b[0][r + (size_t)(c0 + q) * wk.ld[0]] = mine[r + (size_t)q * kGT_LDS];
+                __syncwarp();
+            }
+            __syncthreads();
+            return;
+        }
+        // (N = 144: the chain runs in the shared-memory staging tile, idle at this point, and is copied out at the end)
+        double* X = wk.stage ? wk.stage : wk.b[0];
+        const int ldx = wk.stage ? wk.lds : wk.ld[0];
         __syncthreads();
         for (int e = threadIdx.x; e < n * n; e += blockDim.x) {  // B_{l0} = diag(ev) expK
             const int r = e % n, c = e / n;
@@ -310,6 +344,11 @@ __device__ void dev_bbar(const Params& p, Work& wk, int walker, int i_stack) {
             for (int i = threadIdx.x; i < n; i += blockDim.x) ev[i] = p.lut_ev[f[(size_t)l * n + i]];
             __syncthreads();
             cta_kron<false, 4>(X, ldx, n, p.kL1, p.kL2, p.kg, p.kg + 256, nullptr, ev);
+        }
+        if (wk.stage) {
+            __syncthreads();
+            cta_copy(wk.b[0], wk.ld[0], X, ldx, n);
+            __syncthreads();
         }
         return;
     }

@@ -100,6 +100,8 @@ __device__ __noinline__ void cta_gemm_tma256(double* __restrict__ C, int ldc, co
             }
             __syncthreads();  // all warps are done with As[buf] (and, after the last k-panel, with Bs)
         }
+        // scalings, then (accumulating with scalings) all loads of C before the first store: independent L2 accesses instead of
+        // a load-add-store chain per element
 #pragma unroll
         for (int m = 0; m < 4; ++m) {
             const int r = r0 + 8 * m + gr;
@@ -112,11 +114,16 @@ __device__ __noinline__ void cta_gemm_tma256(double* __restrict__ C, int ldc, co
                     double v = acc[m][q][j];
                     if (rs) v *= rsv;
                     if (cs) v *= cs[c];
-                    double* dst = C + r + (size_t)c * ldc;
-                    if (accumulate && !preload) v += *dst;
-                    *dst = v;
+                    if (accumulate && !preload) v += C[r + (size_t)c * ldc];
+                    acc[m][q][j] = v;
                 }
         }
+#pragma unroll
+        for (int m = 0; m < 4; ++m)
+#pragma unroll
+            for (int q = 0; q < 8; ++q)
+#pragma unroll
+                for (int j = 0; j < 2; ++j) C[(r0 + 8 * m + gr) + (size_t)(c0 + 8 * q + 2 * tg + j) * ldc] = acc[m][q][j];
     }
     __syncthreads();
     if (tid == 0) {

@@ -459,7 +459,12 @@ static size_t plan_stab_smem(Params& p, int n) {
     const size_t tile = (size_t)n * p.LD * 8;
     p.smem_mats_stab = (sb + 3 * tile <= (size_t)kMaxSmem) ? 3 : 0;
     p.smem_stage = (!p.smem_arena && p.smem_mats_stab == 0 && sb + tile <= (size_t)kMaxSmem) ? 1 : 0;
-    return sb + (p.smem_mats_stab + p.smem_stage) * tile + (p.smem_arena ? kGemmTmaArenaBytes : 0);
+    // beside the staging tile: a right-hand-side panel for the triangular solves (n = 144: 28 KB)
+    const size_t rhs = (size_t)(n + 4) * kRhsPanelCols * 8;
+    const char* np_ = getenv("DQMCB_NO_RHS_PANEL");
+    p.smem_rhs = (p.smem_stage && (n & 15) == 0 && n % kRhsPanelCols == 0 && (n & 7) == 0 && sb + tile + rhs <= (size_t)kMaxSmem &&
+                  !(np_ && np_[0] == (char)49)) ? 1 : 0;
+    return sb + (p.smem_mats_stab + p.smem_stage) * tile + (p.smem_arena ? kGemmTmaArenaBytes : 0) + (p.smem_rhs ? rhs : 0);
 }
 
 static size_t prop_small_bytes(int n) {

@@ -19,6 +19,7 @@ struct Params {
     int smem_mats_prop;  // how many N x LD matrices of the propagate kernel live in SMEM (0..2)
     int smem_mats_stab;  // ... of the stabilisation kernels (0 or 3)
     int smem_stage;      // 1: no resident tiles but one shared-memory staging tile for the factorisations
+    int smem_rhs;        // 1: beside the staging tile, a 24-column right-hand-side panel for cta_lu_solve_panels (N = 144)
     int smem_arena;      // 1: neither fits (N = 256): shared memory holds the operand panels of the TMA-staged product (gemm_tma.cuh)
     int delay_k;         // > 1: delayed rank-k Metropolis updates in the generic propagate kernel
     int w0, w1;          // walker range [w0, w1) of this launch (walker groups on separate streams)

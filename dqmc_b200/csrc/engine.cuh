@@ -15,6 +15,8 @@ namespace dq {
 // --------------------------------------------------------------------------------------------------
 // per-CTA workspace carved out of dynamic shared memory (+ global fallback for the big tiles)
 // --------------------------------------------------------------------------------------------------
+constexpr int kRhsPanelCols = 24;  // right-hand-side panel of the N = 144 solves: 144 = 6 x 24, 148 x 24 doubles = 28 KB beside the staging tile
+
 struct Work {
     double* b[3];  // N x LD tiles
     int ld[3];
@@ -23,6 +25,8 @@ struct Work {
     double *tau, *vn1, *vn2, *sv[4], *dnew, *prow, *jrow, *red;
     int *jpvt, *ipiv, *info;
     unsigned char* arena;  // operand panels of cta_gemm_tma256 (N = 256), else null
+    double* rhs_panel;     // 24-column right-hand-side panel of cta_lu_solve_panels (N = 144), else null
+    int rhs_ld;
 };
 
 __host__ __device__ inline size_t small_bytes(int N) {
@@ -51,6 +55,8 @@ __device__ inline void carve(Work& wk, const Params& p, int walker, int nmats_sm
     wk.stage = (nmats_smem == 0 && p.smem_stage) ? tiles : nullptr;
     wk.lds = p.LD;
     wk.arena = (nmats_smem == 0 && !p.smem_stage && p.smem_arena) ? reinterpret_cast<unsigned char*>(tiles) : nullptr;
+    wk.rhs_ld = N + 4;
+    wk.rhs_panel = (wk.stage && p.smem_rhs) ? tiles + (size_t)N * p.LD : nullptr;
     double* gws = p.ws + (size_t)walker * 3 * N * p.LD;
     for (int i = 0; i < 3; ++i) {
         if (i < nmats_smem) {
@@ -76,10 +82,12 @@ __device__ __forceinline__ void dev_gemm(const Work& wk, double* C, int ldc, con
 }
 
 // Solve with a cta_lu factorisation on a right-hand side written with its rows already interchanged.
-__device__ __forceinline__ void dev_lu_solve_prepermuted(const Work& wk, const double* A, int lda, int n, double* Bm, int ldb) {
+__device__ __forceinline__ void dev_lu_solve_prepermuted(const Work& wk, double* A, int lda, int n, double* Bm, int ldb) {
     if (wk.arena && n == kGT_N && blockDim.x == 256 && !(lda & 1) && !(ldb & 1) &&
         !((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(Bm)) & 15))
         cta_lu_solve_tma256(A, lda, Bm, ldb, wk.arena);
+    else if (wk.rhs_panel && (n & 15) == 0 && n % kRhsPanelCols == 0)
+        cta_lu_solve_panels<kRhsPanelCols>(A, lda, n, Bm, ldb, wk.rhs_panel, wk.rhs_ld, wk.prow);
     else
         cta_lu_solve(A, lda, n, wk.ipiv, Bm, 1, ldb, true);
 }

@@ -81,6 +81,9 @@ __device__ __forceinline__ void dev_gemm(const Work& wk, double* C, int ldc, con
         cta_gemm<ACC>(C, ldc, A, rsA, csA, B, rsB, csB, n, rs, cs);
 }
 
+// shared-memory staging of cta_lu_blocked's panel and block row: the operand arena, when the walker has one (N = 256)
+__device__ __forceinline__ double* lu_staging(const Work& wk) { return wk.arena ? reinterpret_cast<double*>(wk.arena + 64) : nullptr; }
+
 // Solve with a cta_lu factorisation on a right-hand side written with its rows already interchanged.
 __device__ __forceinline__ void dev_lu_solve_prepermuted(const Work& wk, double* A, int lda, int n, double* Bm, int ldb) {
     if (wk.arena && n == kGT_N && blockDim.x == 256 && !(lda & 1) && !(ldb & 1) &&
@@ -196,7 +199,7 @@ __device__ double dev_inv_I_plus_ldr(const Params& p, Work& wk, int n, const dou
     double* f0 = b0;
     int lf0 = l0;
     stage_in(wk, n, f0, lf0);
-    cta_lu(f0, lf0, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    cta_lu(f0, lf0, n, wk.ipiv, wk.prow, wk.jrow, wk.info, lu_staging(wk));
     note_fail(p, wk, 10);
     set_diag(b1, l1, n, wk.sv[0]);
     __syncthreads();
@@ -212,7 +215,7 @@ __device__ double dev_inv_I_plus_ldr(const Params& p, Work& wk, int n, const dou
     f0 = b0;
     lf0 = l0;
     stage_in(wk, n, f0, lf0);
-    cta_lu(f0, lf0, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    cta_lu(f0, lf0, n, wk.ipiv, wk.prow, wk.jrow, wk.info, lu_staging(wk));
     note_fail(p, wk, 11);
     part = 0.0;
     for (int i = threadIdx.x; i < n; i += blockDim.x) part += log(fabs(f0[i + (size_t)i * lf0]));
@@ -240,7 +243,7 @@ __device__ void dev_inv_I_plus_ldr_mul_ldr(const Params& p, Work& wk, int n, con
     cta_copy(f0, lf0, R2, ldg, n);
     __syncthreads();
     DQ_PH(p, 5);
-    cta_lu(f0, lf0, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    cta_lu(f0, lf0, n, wk.ipiv, wk.prow, wk.jrow, wk.info, lu_staging(wk));
     DQ_PH(p, 6);
     note_fail(p, wk, 12);
     // right-hand side D2_large^-1 written with its rows already interchanged: (P D)(i, c) = D(perm[i], c)
@@ -271,7 +274,7 @@ __device__ void dev_inv_I_plus_ldr_mul_ldr(const Params& p, Work& wk, int n, con
     int lf2 = l2;
     stage_in(wk, n, f2, lf2);
     DQ_PH(p, 9);
-    cta_lu(f2, lf2, n, wk.ipiv, wk.prow, wk.jrow, wk.info);
+    cta_lu(f2, lf2, n, wk.ipiv, wk.prow, wk.jrow, wk.info, lu_staging(wk));
     DQ_PH(p, 10);
     note_fail(p, wk, 13);
     // RHS = D1l^-1 L1^T  -> b0      (rhs_mode 1: RHS = D1s R1, stablelinalg::inv_invldr_plus_ldr,

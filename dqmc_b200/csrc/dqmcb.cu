@@ -667,7 +667,10 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
         // exp(+dtau K) to 1e-14 of their largest entry and are symmetric (the right products use the transposed view).
         const char* nk = getenv("DQMCB_NO_KRON");
         std::vector<int> cand;
-        for (int a = 1; a <= 16; ++a)
+        // Lattices below 7 x 7 keep the dense products: the run-time-masked routine (no compile-time extents there) costs more
+        // than 4 N^3 flops of plain FMA tiles at that size (measured at 6 x 6: propagate 1.00 -> 0.76 ms, stabilize 0.59 -> 0.50 ms
+        // per launch; at 10 x 10 and 14 x 14 the structured products win by 10-15%).
+        for (int a = 1; a <= 16 && N > 48; ++a)
             if (N % a == 0 && N / a <= 16) cand.push_back(a);
         std::sort(cand.begin(), cand.end(), [&](int a, int b) { return std::abs(a - N / a) < std::abs(b - N / b) || (std::abs(a - N / a) == std::abs(b - N / b) && a > b); });
         for (size_t ci = 0; ci < cand.size() && !p.kg && !(nk && nk[0] == (char)49) && expK[0] != 0.0 && invexpK[0] != 0.0; ++ci) {

@@ -322,6 +322,51 @@ def test_kronecker_factor_path_equals_dense_path(monkeypatch):
     assert rel_err(fallback[0], dense[0]) < 1e-7
 
 
+def test_runtime_masked_kronecker_path_on_a_10x6_lattice(monkeypatch):
+    """Lattices that are neither 8x8, 12x12 nor 16x16 take the RUN-TIME masked Kronecker routine of the generic engine when
+    N > 48 (below that the dense products are faster and are what runs: C0, R7).  10 x 6 (N = 60, extents that are not
+    multiples of 4 or 8 in either direction): block product and one wrap against the dense path to 1e-12 / 1e-10 and
+    against the oracle, identical decisions over a free-running sweep."""
+    from dqmc_b200 import capi
+
+    cfg = (10, 6, 4.0, 1.0, 0.1, 1.5, 15, 5)
+    W = 4
+    m, d = make_oracle(cfg, 3)
+    rng = np.random.default_rng(23)
+    f0 = rng.integers(0, 4, size=(W, cfg[6], cfg[0] * cfg[1]), dtype=np.int8)
+    out = []
+    for env in (None, "1"):
+        if env is None:
+            monkeypatch.delenv("DQMCB_NO_KRON", raising=False)
+        else:
+            monkeypatch.setenv("DQMCB_NO_KRON", env)
+        ctx = make_ctx(cfg, W, m.expK, m.invexpK)
+        ctx.set_fields(f0)
+        ctx.rng_mode(capi.RNG_PHILOX, 78)
+        ctx.init_stacks()
+        ctx.init_greenfunctions()
+        B = ctx.block_product(1)
+        G0 = ctx.get_G()
+        ctx.wrap_forward(0)
+        Gw = ctx.get_G()
+        ctx.init_greenfunctions()
+        ctx.sweep_0_to_beta()
+        ctx.sweep_beta_to_0()
+        out.append((B, Gw, ctx.get_fields(), ctx.get_G(), ctx.get_stats()[0], G0))
+        ctx.close()
+    kron, dense = out
+    assert rel_err(kron[0], dense[0]) < 1e-12 and rel_err(kron[1], dense[1]) < TOL
+    assert not np.array_equal(kron[0], dense[0])  # the factor path really ran (different rounding order)
+    assert np.array_equal(kron[2], dense[2]) and np.array_equal(kron[4], dense[4])
+    assert rel_err(kron[3], dense[3]) < 1e-9
+    # against the oracle: block product of block 1 and the start-up G of walker 0
+    m.fields = f0[0].astype(np.int64).copy()
+    assert rel_err(kron[0][0], d.calculate_Bbar(1)) < 1e-12
+    d.init_stacks()
+    d.init_greenfunctions()
+    assert rel_err(kron[5][0], d.G) < TOL
+
+
 @pytest.mark.parametrize("engine", ["fast", "generic"])
 def test_product_form_matrix_that_is_not_symmetric_takes_the_dense_path(engine, monkeypatch):
     """The row-wise Kronecker passes feed F(gr, tg) where F(tg, gr) is meant: they need SYMMETRIC factors.  A caller-supplied

@@ -1,5 +1,7 @@
 // Development harness: to_LDR (pivoted QR + R scaling + Q formation) of the generic engine alone, in a translation unit that
 // compiles in well under a minute.  extern "C" qr_mini(n, batch, dM, dL, dd, dR, ws): device pointers, ws = batch*3*n*LD doubles.
+#define DQ_TOLDR_PROF 1
+#include <cstdio>
 #include "../../dqmc_b200/csrc/dqmcb_internal.cuh"
 #include "../../dqmc_b200/csrc/engine.cuh"
 using namespace dq;
@@ -28,5 +30,9 @@ extern "C" int qr_mini(int n, int batch, const double* dM, double* dL, double* d
     const size_t smem = sb + (p.smem_mats_stab + p.smem_stage) * tile;
     cudaFuncSetAttribute(k_mini, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     k_mini<<<batch, kThreads, smem>>>(p, dM, dL, dd, dR);
+    cudaDeviceSynchronize();
+    long long h[8];
+    cudaMemcpyFromSymbol(h, g_toldr_prof, sizeof(h));
+    printf("to_LDR phases (CTA 0, cycles): stage_in %lld, QR %lld, d + R %lld, form Q %lld\n", h[1] - h[0], h[2] - h[1], h[3] - h[2], h[4] - h[3]);
     return (int)cudaGetLastError();
 }

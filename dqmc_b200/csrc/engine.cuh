@@ -132,11 +132,21 @@ __device__ inline void stage_in(Work& wk, int n, double*& F, int& ldf) {
     }
 }
 
+// (benchmarks/qrdev compiles this with DQ_TOLDR_PROF to stamp the phases; no code otherwise)
+#ifdef DQ_TOLDR_PROF
+__device__ long long g_toldr_prof[8];
+#define DQ_TL(k) do { __syncthreads(); if (threadIdx.x == 0 && blockIdx.x == 0) g_toldr_prof[k] = clock64(); } while (0)
+#else
+#define DQ_TL(k) do { } while (0)
+#endif
 __device__ void dev_to_ldr(Work& wk, int n, double* A, int lda, double* Qo, int ldq, double* Ro, int ldr, double* dout) {
     __syncthreads();
+    DQ_TL(0);
     stage_in(wk, n, A, lda);
+    DQ_TL(1);
     int* list = reinterpret_cast<int*>(wk.jrow);  // n doubles = 2 n ints: active-column list and its inverse map
     cta_qrp(A, lda, n, wk.tau, wk.jpvt, wk.vn1, wk.vn2, list, list + n);
+    DQ_TL(2);
     // column jpvt[j] of A holds R(0..j, j) (and the reflector below): d_j = |R(j,j)|, and R_final = (D^-1 R) P^T puts
     // that column back at index jpvt[j] -- where it already is
     for (int j = threadIdx.x; j < n; j += blockDim.x) {
@@ -151,8 +161,10 @@ __device__ void dev_to_ldr(Work& wk, int n, double* A, int lda, double* Qo, int 
         const int i = e % n, c = e / n;
         Ro[i + (size_t)c * ldr] = (i <= wk.ipiv[c]) ? wk.vn1[i] * A[i + (size_t)c * lda] : 0.0;
     }
+    DQ_TL(3);
     cta_form_q(Qo, ldq, A, lda, wk.tau, n, wk.jpvt);
     __syncthreads();
+    DQ_TL(4);
 }
 
 // split d into D_large^-1 (or D_large) and D_small (source/stablelinalg.cpp:100-108)

@@ -563,13 +563,24 @@ __device__ int dev_local_update_delayed(const Params& p, int n, double* g, int l
         const double prob = fmin(1.0, fabs(R));
         if (s_u[idx] < prob) {
             ++accepted;
-            const double pref = delta / r;
+            const double pref = delta * rcp_newton(r);  // <= 1 ulp from delta / r, off the IEEE division's ~150-cycle chain
             for (int t = threadIdx.x; t < n; t += blockDim.x) {
                 double uc = g[t + (size_t)i * ldg], vr = g[i + (size_t)t * ldg];
-                for (int m = 0; m < cnt; ++m) {
+                // pending factors, two independent accumulation chains per sum (the loads of a step overlap the FMAs of the other)
+                double uc1 = 0.0, vr1 = 0.0;
+                int m = 0;
+                for (; m + 1 < cnt; m += 2) {
+                    uc = fma(dU[m * n + t], dV[m * n + i], uc);
+                    vr = fma(dU[m * n + i], dV[m * n + t], vr);
+                    uc1 = fma(dU[(m + 1) * n + t], dV[(m + 1) * n + i], uc1);
+                    vr1 = fma(dU[(m + 1) * n + i], dV[(m + 1) * n + t], vr1);
+                }
+                if (m < cnt) {
                     uc = fma(dU[m * n + t], dV[m * n + i], uc);
                     vr = fma(dU[m * n + i], dV[m * n + t], vr);
                 }
+                uc += uc1;
+                vr += vr1;
                 if (t == i) vr -= 1.0;
                 const double us = pref * uc;
                 dU[cnt * n + t] = us;

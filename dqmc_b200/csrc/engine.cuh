@@ -145,7 +145,7 @@ __device__ void dev_to_ldr(Work& wk, int n, double* A, int lda, double* Qo, int 
     stage_in(wk, n, A, lda);
     DQ_TL(1);
     int* list = reinterpret_cast<int*>(wk.jrow);  // n doubles = 2 n ints: active-column list and its inverse map
-    cta_qrp(A, lda, n, wk.tau, wk.jpvt, wk.vn1, wk.vn2, list, list + n);
+    cta_qrp(A, lda, n, wk.tau, wk.jpvt, wk.vn1, wk.vn2, list, list + n, wk.prow);  // prow: second buffer of the partial norms
     DQ_TL(2);
     // column jpvt[j] of A holds R(0..j, j) (and the reflector below): d_j = |R(j,j)|, and R_final = (D^-1 R) P^T puts
     // that column back at index jpvt[j] -- where it already is

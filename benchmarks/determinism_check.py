@@ -13,7 +13,10 @@ CASES = [  # name, L1, L2, U, beta, nt, n_stab, W, delay_k, sweeps
     ("R7 generic N=35", 7, 5, 3.0, 3.0, 23, 6, 1500, 0, 6),
     ("C2 generic N=144 k=32", 12, 12, 4.0, 2.0, 20, 10, 296, 32, 3),
     ("C2 generic N=144 k=8", 12, 12, 4.0, 2.0, 20, 10, 296, 8, 3),
+    ("C2 generic N=144 k=16", 12, 12, 4.0, 2.0, 20, 10, 296, 16, 3),
     ("C3 generic N=256 k=32", 16, 16, 4.0, 1.0, 10, 5, 148, 32, 2),
+    ("C3 generic N=256 k=32, 1.5 waves", 16, 16, 6.0, 1.0, 10, 5, 222, 32, 2),
+    ("10x6 generic N=60 (run-time Kronecker)", 10, 6, 4.0, 1.5, 15, 5, 600, 0, 4),
 ]
 
 def run(case, streams):

@@ -1743,7 +1743,7 @@ static int run_ldr_op(int device, int n, int batch, int op, const double* M, con
     p.N = n;
     const size_t smem = plan_stab_smem(p, n);
     p.W = batch;
-    const size_t nn = (size_t)n * n, tile = (size_t)n * p.LD * 8;
+    const size_t nn = (size_t)n * n;
     std::vector<void*> allocs;
     int rc = DQMCB_OK;
     auto up = [&](const double* h, size_t cnt) -> double* {

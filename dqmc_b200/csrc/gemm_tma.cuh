@@ -188,7 +188,7 @@ __device__ __noinline__ void cta_lu_solve_tma256(const double* __restrict__ A, i
                 *reinterpret_cast<double2*>(Xs + 2 * r2 + (size_t)c * LDS) = *reinterpret_cast<const double2*>(Bm + 2 * r2 + (size_t)(c0 + c) * ldb);
             }
         }
-        long long tp_ = DQ_T0();
+        [[maybe_unused]] long long tp_ = DQ_T0();
         if (buf == 0) {
             mbar_wait(bar + 1, par0);
             par0 ^= 1;

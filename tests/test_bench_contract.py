@@ -47,6 +47,22 @@ def test_reference_arm_line():
     assert d["e2e"]["value"] == d["value"] and d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
 
 
+def test_reference_arm_under_torchrun_prints_one_line_from_rank_0():
+    """N > 1: the driver launches the reference arm under torchrun like the product arm; rank 0 alone runs and prints, the
+    other ranks exit 0 without work."""
+    ref = os.path.join(ROOT, "oracle", "_ref", "libdqmc_ref.so")
+    if not os.path.exists(ref) and not os.path.isdir("/root/reference"):
+        pytest.skip("oracle/_ref not built and the reference sources are not on this machine")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29571", os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1", "--warmup", "1"]
+    r = subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [ln for ln in r.stdout.splitlines() if ln.strip().startswith("{")]
+    assert len(lines) == 1
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["value"] > 0
+
+
 @pytest.mark.gpu
 def test_product_arm_line():
     """`bench.py` on one GPU (short: 3 steps, 3 warm-up, 2 thermalisation sweeps, no CPU leg)."""

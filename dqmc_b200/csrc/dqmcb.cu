@@ -51,8 +51,8 @@ __global__ void __launch_bounds__(kThreads, BIG ? 1 : 2) k_propagate(Params p, i
     double* t = (p.smem_mats_prop >= 2) ? tiles + (size_t)n * p.LD : gws + (size_t)n * p.LD;
     // delayed-update factors U, V (K x n each) + running diagonal (2 copies), behind the resident tiles
     double* dU = tiles + (size_t)p.smem_mats_prop * n * p.LD;
-    double* dV = dU + (size_t)p.delay_k * n;
-    double* s_diag = dV + (size_t)p.delay_k * n;
+    double* dV = dU + (size_t)p.delay_k * delay_ld(n);
+    double* s_diag = dV + (size_t)p.delay_k * delay_ld(n);
     const int ld = p.LD;
     double* Gg = p.G + (size_t)w * n * n;
     cta_copy(g, ld, Gg, n, n);
@@ -738,7 +738,7 @@ int dqmcb_create(const dqmcb_config* cfg, const double* expK, const double* inve
     ctx->smem_stab = stab_smem;
     p.delay_k = (cfg->delay_k > 1) ? std::min(cfg->delay_k, 64) : 0;
     const size_t pb = prop_small_bytes(N);
-    const size_t dly = p.delay_k ? ((size_t)2 * p.delay_k * N + 2 * N) * 8 : 0;
+    const size_t dly = p.delay_k ? ((size_t)2 * p.delay_k * delay_ld(N) + 2 * N) * 8 : 0;
     p.smem_mats_prop = (pb + dly + 2 * tile <= (size_t)kMaxSmem) ? 2 : ((pb + dly + tile <= (size_t)kMaxSmem) ? 1 : 0);
     ctx->smem_prop = pb + dly + p.smem_mats_prop * tile;
     if (ctx->smem_prop > (size_t)kMaxSmem) {

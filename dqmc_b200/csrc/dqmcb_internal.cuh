@@ -14,6 +14,10 @@ constexpr int kThreads = 256;        // threads per CTA of the generic kernels
 constexpr int kMaxSmem = 227 * 1024; // opt-in dynamic shared memory per CTA on sm_100a
 
 // Everything a kernel needs; passed by value (lives in constant bank / param space).
+// leading dimension of the delayed-update factors U (n x K) and V (K x n) in shared memory: n + 4 where n is a multiple of 8,
+// so that the tensor-core fragments of the rank-K flush (lanes spread over 4 consecutive K-indices) hit distinct banks
+__host__ __device__ inline int delay_ld(int n) { return (n % 8 == 0) ? n + 4 : n; }
+
 struct Params {
     int N, LD, nt, n_stab, n_stack, W;
     int smem_mats_prop;  // how many N x LD matrices of the propagate kernel live in SMEM (0..2)

@@ -540,12 +540,13 @@ __device__ int dev_local_update(const Params& p, int n, double* g, int ldg, int8
 // an accept forms the current column / row from G0 and the pending factors (2 n m flops instead of a
 // 2 n^2 sweep over G) and G0 is touched once per K accepts by a rank-K product.  Pays off where G does
 // not sit in registers: N = 144 (G in shared memory) and N = 256 (G in L2 / HBM).
-//   dU[m*n + r] = U(r, m),  dV[m*n + c] = V(m, c),  s_diag[n] running diag(G).
+//   dU[m*ldu + r] = U(r, m),  dV[m*ldu + c] = V(m, c)  (ldu = delay_ld(n)),  s_diag[n] running diag(G).
 // --------------------------------------------------------------------------------------------------
 template <bool BIG = true>
 __device__ int dev_local_update_delayed(const Params& p, int n, double* g, int ldg, int8_t* s_f, const int* s_perm, const int* s_k,
                                         const double* s_u, double* s_diag, double* dU, double* dV, int K) {
     int accepted = 0, cnt = 0;
+    const int ldu = delay_ld(n);
     // running diagonal, double-buffered: an accepting thread writes the other copy, so a warp that is
     // still deciding this (or an earlier, rejected) proposal never sees a half-updated diagonal
     double* dcur = s_diag;
@@ -570,21 +571,21 @@ __device__ int dev_local_update_delayed(const Params& p, int n, double* g, int l
                 double uc1 = 0.0, vr1 = 0.0;
                 int m = 0;
                 for (; m + 1 < cnt; m += 2) {
-                    uc = fma(dU[m * n + t], dV[m * n + i], uc);
-                    vr = fma(dU[m * n + i], dV[m * n + t], vr);
-                    uc1 = fma(dU[(m + 1) * n + t], dV[(m + 1) * n + i], uc1);
-                    vr1 = fma(dU[(m + 1) * n + i], dV[(m + 1) * n + t], vr1);
+                    uc = fma(dU[m * ldu + t], dV[m * ldu + i], uc);
+                    vr = fma(dU[m * ldu + i], dV[m * ldu + t], vr);
+                    uc1 = fma(dU[(m + 1) * ldu + t], dV[(m + 1) * ldu + i], uc1);
+                    vr1 = fma(dU[(m + 1) * ldu + i], dV[(m + 1) * ldu + t], vr1);
                 }
                 if (m < cnt) {
-                    uc = fma(dU[m * n + t], dV[m * n + i], uc);
-                    vr = fma(dU[m * n + i], dV[m * n + t], vr);
+                    uc = fma(dU[m * ldu + t], dV[m * ldu + i], uc);
+                    vr = fma(dU[m * ldu + i], dV[m * ldu + t], vr);
                 }
                 uc += uc1;
                 vr += vr1;
                 if (t == i) vr -= 1.0;
                 const double us = pref * uc;
-                dU[cnt * n + t] = us;
-                dV[cnt * n + t] = vr;
+                dU[cnt * ldu + t] = us;
+                dV[cnt * ldu + t] = vr;
                 dnxt[t] = fma(us, vr, dcur[t]);
             }
             ++cnt;
@@ -594,14 +595,14 @@ __device__ int dev_local_update_delayed(const Params& p, int n, double* g, int l
             __syncthreads();
             if (threadIdx.x == 0) s_f[i] = (int8_t)newf;
             if (cnt == K) {
-                cta_gemm<true, BIG>(g, ldg, dU, 1, n, dV, n, 1, n, nullptr, nullptr, cnt);
+                cta_gemm<true, BIG>(g, ldg, dU, 1, ldu, dV, ldu, 1, n, nullptr, nullptr, cnt);
                 cnt = 0;
                 __syncthreads();
             }
         }
     }
     if (cnt) {
-        cta_gemm<true, BIG>(g, ldg, dU, 1, n, dV, n, 1, n, nullptr, nullptr, cnt);
+        cta_gemm<true, BIG>(g, ldg, dU, 1, ldu, dV, ldu, 1, n, nullptr, nullptr, cnt);
         __syncthreads();
     }
     return accepted;
